@@ -1,0 +1,9 @@
+"""coloc_b200 -- B200-native (sm_100a) front end of CoLoC: pyramid resize, FAST+NMS+orientation,
+512-bit LATCH, brute-force Hamming 2-NN, behind the C ABI in include/coloc_b200.h.
+
+This package is a thin ctypes binding over libcoloc_b200.so for tests and bench.py; the drop-in
+host side for the reference is the C++ shim in coloc_b200/shim/coloc/ (see INTEGRATION.md).
+There is no CPU fallback: using `coloc_b200.api` without the built library raises.
+"""
+from .api import (Detector, Matcher, ClbError, KP_DTYPE, PARTIAL_DTYPE, lib, lib_path, build,  # noqa: F401
+                  launch_count, set_timing, last_kernel_ms, set_param, microbench_pipes)

@@ -1,0 +1,259 @@
+"""ctypes binding of include/coloc_b200.h.  Mirrors the reference's detector / matcher policy
+objects (include/coloc/GPUDetector.hpp, GPUMatcher.hpp): same option fields, same method meaning,
+errors raised as ClbError(code).  Fails loudly if libcoloc_b200.so is missing -- no fallback."""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+KP_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "u1"), ("_p0", "u1", 3),
+                     ("angle", "<f4"), ("scale", "u1"), ("_p1", "u1", 3)])
+PARTIAL_DTYPE = np.dtype([("best_d", "<i4"), ("best_i", "<i4"), ("second_d", "<i4"), ("_pad", "<i4")])
+assert KP_DTYPE.itemsize == 20 and PARTIAL_DTYPE.itemsize == 16
+
+OK, EINVAL, ECUDA, ECAPACITY, ENOMEM, EUNSUPPORTED = range(6)
+
+
+class ClbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"clb error {code}: {msg}")
+        self.code = code
+
+
+class DetectorOpts(C.Structure):
+    _fields_ = [("scale_factor", C.c_float), ("scale_levels", C.c_int32), ("width", C.c_int32),
+                ("height", C.c_int32), ("maxkp", C.c_int32), ("thresh", C.c_int32)]
+
+
+class MatcherOpts(C.Structure):
+    _fields_ = [("distRatio", C.c_float), ("thresh", C.c_int32), ("maxkp", C.c_int32)]
+
+
+def lib_path():
+    return os.path.join(HERE, "libcoloc_b200.so")
+
+
+def build():
+    """compile the CUDA extension in-tree (nvcc, sm_100a)."""
+    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "csrc")])
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise ImportError(f"{p} is not built: run `make -C coloc_b200/csrc` (or __graft_entry__.build()); "
+                              "coloc_b200 has no CPU fallback")
+        L = C.CDLL(p)
+        L.clb_strerror.restype = C.c_char_p
+        L.clb_last_error.restype = C.c_char_p
+        L.clb_launch_count.restype = C.c_int64
+        L.clb_last_kernel_ms.restype = C.c_float
+        L.clb_last_kernel_ms.argtypes = [C.c_char_p]
+        L.clb_set_param.argtypes = [C.c_char_p, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        L = lib()
+        raise ClbError(rc, f"{L.clb_strerror(rc).decode()} ({L.clb_last_error().decode()})")
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def launch_count():
+    return int(lib().clb_launch_count())
+
+
+def set_timing(on):
+    lib().clb_set_timing(int(bool(on)))
+
+
+def last_kernel_ms(which):
+    return float(lib().clb_last_kernel_ms(which.encode()))
+
+
+def set_param(name, value):
+    _check(lib().clb_set_param(name.encode(), int(value)))
+
+
+def microbench_pipes(device=0):
+    out = (C.c_double * 6)()
+    _check(lib().clb_microbench_pipes(int(device), out))
+    k = ["popc_per_clk_sm", "lop3_per_clk_sm", "mixed_popc_per_clk_sm", "mixed_lop3_per_clk_sm", "sm_mhz", "sm_count"]
+    return dict(zip(k, [float(v) for v in out]))
+
+
+def _dptr(t):
+    """device pointer of a torch CUDA tensor (plumbing only); ints pass through."""
+    if t is None:
+        return C.c_void_p(0)
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    return C.c_void_p(t.data_ptr())
+
+
+class Detector:
+    """GPUDetector (include/coloc/GPUDetector.hpp:29-292) over the C ABI."""
+
+    def __init__(self, width, height, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0):
+        self.opts = DetectorOpts(scale_factor, scale_levels, width, height, maxkp, thresh)
+        self._h = C.c_void_p()
+        _check(lib().clb_detector_create(C.byref(self.opts), int(device), C.byref(self._h)))
+        self.kps = np.zeros(0, KP_DTYPE)      # last frame's raw output, as GPUDetector.hpp:32-33
+        self.desc = np.zeros((0, 8), np.uint64)
+
+    def close(self):
+        if self._h:
+            lib().clb_detector_destroy(self._h)
+            self._h = C.c_void_p()
+
+    freeGPUMemory = close
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def level_dims(self, w, h):
+        n = self.opts.scale_levels
+        ws = np.zeros(n, np.int32); hs = np.zeros(n, np.int32); fs = np.zeros(n, np.float32)
+        _check(lib().clb_detector_level_dims(self._h, w, h, _ptr(ws), _ptr(hs), _ptr(fs)))
+        return ws.tolist(), hs.tolist(), fs
+
+    def detect_and_describe(self, img, cap=None):
+        """GPUDetector::detectAndDescribe (GPUDetector.hpp:216-291) on a host uint8 image."""
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        cap = cap if cap is not None else self.opts.maxkp
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 8), np.uint64)
+        n = C.c_int(0)
+        _check(lib().clb_detect_describe(self._h, _ptr(img), w, h, img.strides[0], _ptr(kps), _ptr(desc), cap, C.byref(n)))
+        self.kps, self.desc = kps[:n.value], desc[:n.value]
+        return self.kps, self.desc
+
+    def detect_and_describe_dev(self, d_img, stream=None):
+        """device-resident variant: torch uint8 CUDA tensor in, (d_kps ptr, d_desc ptr, n) out."""
+        h, w = d_img.shape
+        pk = C.c_void_p(); pd = C.c_void_p(); n = C.c_int(0)
+        _check(lib().clb_detect_describe_dev(self._h, _dptr(d_img), w, h, d_img.stride(0), C.byref(pk), C.byref(pd), C.byref(n),
+                                             C.c_void_p(stream or 0)))
+        return pk.value, pd.value, n.value
+
+    def pyramid(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        ws, hs, _ = self.level_dims(w, h)
+        out = np.zeros(sum(a * b for a, b in zip(ws, hs)), np.uint8)
+        _check(lib().clb_pyramid(self._h, _ptr(img), w, h, img.strides[0], _ptr(out)))
+        lv, off = [], 0
+        for a, b in zip(ws, hs):
+            lv.append(out[off:off + a * b].reshape(b, a)); off += a * b
+        return lv
+
+    def fast_nms_angle(self, level, level_idx=0, cap=None):
+        level = np.ascontiguousarray(level, np.uint8)
+        h, w = level.shape
+        cap = cap if cap is not None else self.opts.maxkp
+        kps = np.zeros(cap, KP_DTYPE); n = C.c_int(0)
+        _check(lib().clb_fast_nms_angle(self._h, _ptr(level), w, h, level.strides[0], int(level_idx), _ptr(kps), cap, C.byref(n)))
+        return kps[:n.value]
+
+    def describe(self, levels, kps):
+        levels = [np.ascontiguousarray(l, np.uint8) for l in levels]
+        L = len(levels)
+        ptrs = (C.c_void_p * L)(*[l.ctypes.data for l in levels])
+        ws = np.array([l.shape[1] for l in levels], np.int32); hs = np.array([l.shape[0] for l in levels], np.int32)
+        kps = np.ascontiguousarray(kps, KP_DTYPE)
+        desc = np.zeros((len(kps), 8), np.uint64)
+        _check(lib().clb_describe(self._h, ptrs, _ptr(ws), _ptr(hs), _ptr(ws), L, _ptr(kps), len(kps), _ptr(desc)))
+        return desc
+
+    def sincos(self, angles):
+        a = np.ascontiguousarray(angles, np.float32)
+        s = np.zeros_like(a); c = np.zeros_like(a)
+        _check(lib().clb_sincos(self._h, _ptr(a), a.size, _ptr(s), _ptr(c)))
+        return s, c
+
+
+class Matcher:
+    """GPUMatcher (include/coloc/GPUMatcher.hpp:45-272) over the C ABI."""
+
+    def __init__(self, distRatio=0.8, thresh=60, maxkp=5000, device=0):
+        self.opts = MatcherOpts(distRatio, thresh, maxkp)
+        self._h = C.c_void_p()
+        _check(lib().clb_matcher_create(C.byref(self.opts), int(device), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().clb_matcher_destroy(self._h)
+            self._h = C.c_void_p()
+
+    freeGPUMemory = close
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @staticmethod
+    def _rows(a):
+        a = np.ascontiguousarray(a, np.uint64).reshape(-1, 8)
+        return a, len(a)
+
+    def _outs(self, nQ, want_dist):
+        m = np.zeros(nQ, np.int32)
+        b = np.zeros(nQ, np.int32) if want_dist else None
+        s = np.zeros(nQ, np.int32) if want_dist else None
+        return m, b, s
+
+    def compute_matches(self, Q, T, threshold=40, want_dist=False):
+        """GPUMatcher::computeMatches(hQ, hT, nQ, nT, threshold) (GPUMatcher.hpp:180-226): int match[nQ]."""
+        Q, nQ = self._rows(Q); T, nT = self._rows(T)
+        m, b, s = self._outs(nQ, want_dist)
+        _check(lib().clb_match_2nn(self._h, _ptr(Q), nQ, _ptr(T), nT, int(threshold), _ptr(m), _ptr(b), _ptr(s)))
+        return (m, b, s) if want_dist else m
+
+    def compute_matches_ratio(self, Q, T, ratio=None, want_dist=False):
+        """ratio-test mode of the CPU build (CPUMatcher.hpp:67-76, matching_filters.hpp:39-60)."""
+        Q, nQ = self._rows(Q); T, nT = self._rows(T)
+        m, b, s = self._outs(nQ, want_dist)
+        r = self.opts.distRatio if ratio is None else ratio
+        _check(lib().clb_match_2nn_ratio(self._h, _ptr(Q), nQ, _ptr(T), nT, C.c_float(r), _ptr(m), _ptr(b), _ptr(s)))
+        return (m, b, s) if want_dist else m
+
+    def set_map_data(self, M):
+        """GPUMatcher::setMapData (GPUMatcher.hpp:110-117)."""
+        M, nM = self._rows(M)
+        _check(lib().clb_set_map(self._h, _ptr(M), nM))
+
+    def match_with_map(self, Q, threshold=-1, want_dist=False):
+        """setQueryImage + matchFeaturesWithMap (GPUMatcher.hpp:130-141,252-271); returns MAP row per query."""
+        Q, nQ = self._rows(Q)
+        m, b, s = self._outs(nQ, want_dist)
+        _check(lib().clb_match_map(self._h, _ptr(Q), nQ, int(threshold), _ptr(m), _ptr(b), _ptr(s)))
+        return (m, b, s) if want_dist else m
+
+    # ---- device-pointer entry points (torch CUDA tensors as plain buffers) -----------------
+    def match_dev(self, dQ, nQ, dT, nT, threshold, d_match, d_best=None, d_second=None, stream=None):
+        _check(lib().clb_match_2nn_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), int(threshold),
+                                       _dptr(d_match), _dptr(d_best), _dptr(d_second), C.c_void_p(stream or 0)))
+
+    def match_partial_dev(self, dQ, nQ, dT, nT, t_base, d_partial, stream=None):
+        _check(lib().clb_match_partial_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), C.c_int64(int(t_base)),
+                                           _dptr(d_partial), C.c_void_p(stream or 0)))
+
+    def merge_partials_dev(self, d_parts, nparts, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
+        _check(lib().clb_merge_partials_dev(self._h, _dptr(d_parts), int(nparts), int(nQ), int(threshold),
+                                            _dptr(d_match), _dptr(d_best), _dptr(d_second), C.c_void_p(stream or 0)))

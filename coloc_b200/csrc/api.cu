@@ -1,0 +1,313 @@
+// api.cu -- the C ABI (include/coloc_b200.h): detector / matcher objects that own device
+// buffers for their lifetime, as the reference's GPUDetector / GPUMatcher do
+// (include/coloc/GPUDetector.hpp:70-155, GPUMatcher.hpp:70-108).
+#include "common.cuh"
+#include <string.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <new>
+
+namespace clb {
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+int g_timing = 0;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms;
+
+int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
+    snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? CLB_ENOMEM : CLB_ECUDA;
+}
+
+static std::mutex g_timer_mu;
+static std::map<std::string, KernelTimer> g_timers;
+KernelTimer& timer(const char* which) {
+    std::lock_guard<std::mutex> lk(g_timer_mu);
+    return g_timers[which];
+}
+}  // namespace clb
+
+using namespace clb;
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+// ------------------------------------------------------------------------------ detector
+struct clb_detector {
+    clb_detector_opts o;
+    int device, sm_count;
+    cudaStream_t stream;
+    DevBuf pyr;          // all levels, packed, 128-B aligned strides
+    DevBuf fast_scratch;
+    DevBuf kps, desc, misc;   // misc: [0] total count
+    DevBuf stage;        // staging for stage-level entry points
+    int* h_total;        // pinned
+    size_t level_off[CLB_MAX_LEVELS];
+};
+
+static void level_dims(const clb_detector_opts& o, int w, int h, int* ws, int* hs, float* fs) {
+    // GPUDetector.hpp:107-114
+    float f = 1.0f;
+    ws[0] = w; hs[0] = h; fs[0] = 1.0f;
+    for (int i = 1; i < o.scale_levels; ++i) {
+        f *= o.scale_factor;
+        ws[i] = (int)(uint32_t)((float)w / f + 0.5f);
+        hs[i] = (int)(uint32_t)((float)h / f + 0.5f);
+        fs[i] = f;
+    }
+}
+
+// lay the levels of a w x h frame out inside d->pyr; returns bytes needed
+static size_t make_table(clb_detector* d, int w, int h, LevelTable& lt) {
+    float fs[CLB_MAX_LEVELS];
+    lt.n = d->o.scale_levels;
+    level_dims(d->o, w, h, lt.w, lt.h, fs);
+    size_t off = 0;
+    for (int i = 0; i < lt.n; ++i) {
+        lt.f[i] = fs[i];
+        lt.stride[i] = align_up(lt.w[i] > 0 ? lt.w[i] : 1, 128);
+        d->level_off[i] = off;
+        off += (size_t)lt.stride[i] * (lt.h[i] > 0 ? lt.h[i] : 1) + 256;
+        off = (off + 255) & ~(size_t)255;
+    }
+    for (int i = 0; i < lt.n; ++i) lt.img[i] = d->pyr.as<uint8_t>() ? d->pyr.as<uint8_t>() + d->level_off[i] : nullptr;
+    return off;
+}
+
+extern "C" {
+
+const char* clb_strerror(int code) {
+    switch (code) {
+        case CLB_OK: return "ok";
+        case CLB_EINVAL: return "invalid argument";
+        case CLB_ECUDA: return "CUDA runtime error";
+        case CLB_ECAPACITY: return "output capacity too small";
+        case CLB_ENOMEM: return "out of device memory";
+        case CLB_EUNSUPPORTED: return "unsupported";
+        default: return "unknown error";
+    }
+}
+const char* clb_last_error(void) { return g_err; }
+int clb_version(void) { return 100; }
+int clb_device_count(int* n_out) { if (!n_out) return CLB_EINVAL; CLB_CUDA(cudaGetDeviceCount(n_out)); return CLB_OK; }
+int64_t clb_launch_count(void) { return g_launches.load(); }
+int clb_set_timing(int on) { g_timing = on; return CLB_OK; }
+float clb_last_kernel_ms(const char* which) { return which ? timer(which).ms() : 0.f; }
+int clb_set_param(const char* name, int value) {
+    if (!name) return CLB_EINVAL;
+    if (!strcmp(name, "match_rq")) { if (value != 0 && value != 1 && value != 2 && value != 4) return CLB_EINVAL; g_match_rq = value; }
+    else if (!strcmp(name, "match_hs")) { if (value < 0 || value > 3) return CLB_EINVAL; g_match_hs = value; }
+    else if (!strcmp(name, "match_chunks")) { if (value < 0) return CLB_EINVAL; g_match_chunks = value; }
+    else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
+    else return CLB_EINVAL;
+    return CLB_OK;
+}
+int clb_microbench_pipes(int device, double* out6) {
+    if (!out6) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(device));
+    return microbench_pipes(out6);
+}
+
+int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector** out) {
+    if (!opts || !out) return CLB_EINVAL;
+    if (opts->scale_levels < 1 || opts->scale_levels > CLB_MAX_LEVELS || opts->width < 1 || opts->height < 1 ||
+        opts->maxkp < 1 || opts->thresh < 0 || opts->thresh > 255 || !(opts->scale_factor >= 1.0f)) {
+        snprintf(g_err, sizeof(g_err), "bad detector options"); return CLB_EINVAL;
+    }
+    CLB_CUDA(cudaSetDevice(device));
+    clb_detector* d = new (std::nothrow) clb_detector();
+    if (!d) return CLB_ENOMEM;
+    d->o = *opts; d->device = device; d->h_total = nullptr;
+    cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, device);
+    cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMallocHost(&d->h_total, 64);
+    LevelTable lt;
+    size_t bytes = make_table(d, opts->width, opts->height, lt);
+    if (e == cudaSuccess) e = d->pyr.reserve(bytes);
+    make_table(d, opts->width, opts->height, lt);
+    if (e == cudaSuccess) e = d->fast_scratch.reserve(fast_scratch_bytes(lt));
+    if (e == cudaSuccess) e = d->kps.reserve((size_t)opts->maxkp * sizeof(clb_keypoint));
+    if (e == cudaSuccess) e = d->desc.reserve((size_t)opts->maxkp * 64);
+    if (e == cudaSuccess) e = d->misc.reserve(256);
+    if (e != cudaSuccess) { int rc = set_cuda_error(e, "detector allocation", __FILE__, __LINE__); clb_detector_destroy(d); return rc; }
+    int rc = latch_init();
+    if (rc) { clb_detector_destroy(d); return rc; }
+    *out = d;
+    return CLB_OK;
+}
+
+void clb_detector_destroy(clb_detector* d) {
+    if (!d) return;
+    cudaSetDevice(d->device);
+    d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release();
+    if (d->h_total) cudaFreeHost(d->h_total);
+    if (d->stream) cudaStreamDestroy(d->stream);
+    delete d;
+}
+
+int clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, int32_t* hs, float* fs) {
+    if (!d || !ws || !hs) return CLB_EINVAL;
+    float tmp[CLB_MAX_LEVELS];
+    level_dims(d->o, w, h, ws, hs, fs ? fs : tmp);
+    return CLB_OK;
+}
+
+static int check_frame(clb_detector* d, int w, int h, int stride) {
+    if (!d || w < 1 || h < 1 || stride < w) { snprintf(g_err, sizeof(g_err), "bad frame geometry"); return CLB_EINVAL; }
+    if (w > d->o.width || h > d->o.height) { snprintf(g_err, sizeof(g_err), "frame %dx%d exceeds detector size %dx%d", w, h, d->o.width, d->o.height); return CLB_EINVAL; }
+    return CLB_OK;
+}
+
+// device pipeline on a level-0 image already inside d->pyr (table lt)
+static int run_pipeline(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
+    int rc = launch_resize(lt, s);
+    if (rc) return rc;
+    int* d_total = d->misc.as<int>();
+    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    if (rc) return rc;
+    return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s);
+}
+
+int clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h, int stride,
+                            const clb_keypoint** d_kps, const uint64_t** d_desc, int* n_out, void* stream) {
+    int rc = check_frame(d, w, h, stride);
+    if (rc) return rc;
+    if (!d_gray || !n_out) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : d->stream;
+    LevelTable lt;
+    make_table(d, w, h, lt);
+    CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], d_gray, stride, w, h, cudaMemcpyDeviceToDevice, s));
+    rc = run_pipeline(d, lt, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d->misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    *n_out = *d->h_total;
+    if (d_kps) *d_kps = d->kps.as<clb_keypoint>();
+    if (d_desc) *d_desc = d->desc.as<uint64_t>();
+    if (*n_out > d->o.maxkp) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed maxkp %d", *n_out, d->o.maxkp); return CLB_ECAPACITY; }
+    return CLB_OK;
+}
+
+int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int stride,
+                        clb_keypoint* kps_out, uint64_t* desc_out, int cap, int* n_out) {
+    int rc = check_frame(d, w, h, stride);
+    if (rc) return rc;
+    if (!gray || !n_out || cap < 0) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = d->stream;
+    LevelTable lt;
+    make_table(d, w, h, lt);
+    CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], gray, stride, w, h, cudaMemcpyHostToDevice, s));
+    rc = run_pipeline(d, lt, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d->misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    const int n = *d->h_total;
+    *n_out = n;
+    if (n > d->o.maxkp || n > cap) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed capacity (cap %d, maxkp %d)", n, cap, d->o.maxkp); return CLB_ECAPACITY; }
+    if (n > 0) {
+        if (kps_out) CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, s));
+        if (desc_out) CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
+        CLB_CUDA(cudaStreamSynchronize(s));
+    }
+    return CLB_OK;
+}
+
+int clb_pyramid(clb_detector* d, const uint8_t* gray, int w, int h, int stride, uint8_t* levels_out) {
+    int rc = check_frame(d, w, h, stride);
+    if (rc) return rc;
+    if (!gray || !levels_out) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = d->stream;
+    LevelTable lt;
+    make_table(d, w, h, lt);
+    CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], gray, stride, w, h, cudaMemcpyHostToDevice, s));
+    rc = launch_resize(lt, s);
+    if (rc) return rc;
+    size_t off = 0;
+    for (int i = 0; i < lt.n; ++i) {
+        if (lt.w[i] > 0 && lt.h[i] > 0)
+            CLB_CUDA(cudaMemcpy2DAsync(levels_out + off, lt.w[i], lt.img[i], lt.stride[i], lt.w[i], lt.h[i], cudaMemcpyDeviceToHost, s));
+        off += (size_t)lt.w[i] * lt.h[i];
+    }
+    CLB_CUDA(cudaStreamSynchronize(s));
+    return CLB_OK;
+}
+
+int clb_fast_nms_angle(clb_detector* d, const uint8_t* level, int w, int h, int stride, int level_idx,
+                       clb_keypoint* kps_out, int cap, int* n_out) {
+    int rc = check_frame(d, w, h, stride);
+    if (rc) return rc;
+    if (!level || !n_out || level_idx < 0 || level_idx > 255 || cap < 0) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = d->stream;
+    // a one-level table: the image is staged as "level 0" of the detector's pyramid buffer
+    LevelTable lt; memset(&lt, 0, sizeof(lt));
+    lt.n = 1; lt.w[0] = w; lt.h[0] = h; lt.stride[0] = align_up(w, 128); lt.f[0] = 1.f;
+    lt.img[0] = d->pyr.as<uint8_t>();
+    CLB_CUDA(cudaMemcpy2DAsync(d->pyr.p, lt.stride[0], level, stride, w, h, cudaMemcpyHostToDevice, s));
+    int* d_total = d->misc.as<int>();
+    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    const int n = *d->h_total;
+    *n_out = n;
+    if (n > d->o.maxkp || n > cap) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed capacity", n); return CLB_ECAPACITY; }
+    if (n > 0 && kps_out) {
+        CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, s));
+        CLB_CUDA(cudaStreamSynchronize(s));
+        for (int i = 0; i < n; ++i) kps_out[i].scale = (uint8_t)level_idx;
+    }
+    return CLB_OK;
+}
+
+int clb_describe(clb_detector* d, const uint8_t* const* levels, const int32_t* ws, const int32_t* hs,
+                 const int32_t* strides, int nlevels, const clb_keypoint* kps, int n, uint64_t* desc_out) {
+    if (!d || !levels || !ws || !hs || !strides || nlevels < 1 || nlevels > CLB_MAX_LEVELS || n < 0 || (n > 0 && (!kps || !desc_out))) return CLB_EINVAL;
+    if (n > d->o.maxkp) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed maxkp %d", n, d->o.maxkp); return CLB_ECAPACITY; }
+    for (int i = 0; i < n; ++i) if (kps[i].scale >= nlevels || !levels[kps[i].scale]) { snprintf(g_err, sizeof(g_err), "keypoint %d names missing level %d", i, kps[i].scale); return CLB_EINVAL; }
+    if (n == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = d->stream;
+    LevelTable lt; memset(&lt, 0, sizeof(lt));
+    lt.n = nlevels;
+    size_t off = 0;
+    for (int i = 0; i < nlevels; ++i) {
+        lt.w[i] = ws[i]; lt.h[i] = hs[i]; lt.stride[i] = align_up(ws[i] > 0 ? ws[i] : 1, 128); lt.f[i] = 1.f;
+        off += (size_t)lt.stride[i] * (hs[i] > 0 ? hs[i] : 1) + 256;
+    }
+    CLB_CUDA(d->stage.reserve(off));
+    off = 0;
+    for (int i = 0; i < nlevels; ++i) {
+        lt.img[i] = d->stage.as<uint8_t>() + off;
+        if (levels[i] && ws[i] > 0 && hs[i] > 0)
+            CLB_CUDA(cudaMemcpy2DAsync(d->stage.as<uint8_t>() + off, lt.stride[i], levels[i], strides[i], ws[i], hs[i], cudaMemcpyHostToDevice, s));
+        off += (size_t)lt.stride[i] * (hs[i] > 0 ? hs[i] : 1) + 256;
+    }
+    CLB_CUDA(cudaMemcpyAsync(d->kps.p, kps, (size_t)n * sizeof(clb_keypoint), cudaMemcpyHostToDevice, s));
+    int rc = launch_describe(lt, d->kps.as<clb_keypoint>(), n, nullptr, d->o.maxkp, d->desc.as<uint64_t>(), s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    return CLB_OK;
+}
+
+int clb_sincos(clb_detector* d, const float* angles, int n, float* sin_out, float* cos_out) {
+    if (!d || n < 0 || (n > 0 && (!angles || !sin_out || !cos_out))) return CLB_EINVAL;
+    if (n == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t s = d->stream;
+    CLB_CUDA(d->stage.reserve((size_t)n * 12));
+    float* a = d->stage.as<float>();
+    CLB_CUDA(cudaMemcpyAsync(a, angles, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    int rc = launch_sincos(a, n, a + n, a + 2 * (size_t)n, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(sin_out, a + n, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaMemcpyAsync(cos_out, a + 2 * (size_t)n, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    return CLB_OK;
+}
+
+}  // extern "C"

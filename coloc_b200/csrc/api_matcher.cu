@@ -1,0 +1,154 @@
+// api_matcher.cu -- matcher half of the C ABI (include/coloc_b200.h).
+// Mirrors GPUMatcher (include/coloc/GPUMatcher.hpp:45-272): the object owns d_descQ / d_descT /
+// d_descM and the match buffer; host entry points are blocking (copy in, run, copy out, sync).
+#include "common.cuh"
+#include <string.h>
+#include <new>
+
+using namespace clb;
+
+struct clb_matcher {
+    clb_matcher_opts o;
+    int device, sm_count;
+    cudaStream_t stream;
+    DevBuf q, t, map, scratch, out;   // out: match | best | second (3 x nQ int32)
+    int n_map;
+};
+
+static int ensure(clb_matcher* m, int nQ, int nT) {
+    CLB_CUDA(m->scratch.reserve(match_scratch_bytes(nQ, nT)));
+    CLB_CUDA(m->out.reserve((size_t)(nQ > 0 ? nQ : 1) * 12));
+    return CLB_OK;
+}
+
+// shared tail of the host entry points: run on device buffers, copy results out
+static int run_host(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold, float ratio,
+                    int32_t* match_out, int32_t* best_out, int32_t* second_out) {
+    cudaStream_t s = m->stream;
+    int rc = ensure(m, nQ, nT);
+    if (rc) return rc;
+    int32_t* o = m->out.as<int32_t>();
+    rc = launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, ratio,
+                      o, best_out ? o + nQ : nullptr, second_out ? o + 2 * (size_t)nQ : nullptr, nullptr, s);
+    if (rc) return rc;
+    if (match_out) CLB_CUDA(cudaMemcpyAsync(match_out, o, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
+    if (best_out) CLB_CUDA(cudaMemcpyAsync(best_out, o + nQ, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
+    if (second_out) CLB_CUDA(cudaMemcpyAsync(second_out, o + 2 * (size_t)nQ, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    return CLB_OK;
+}
+
+extern "C" {
+
+int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** out) {
+    if (!opts || !out || opts->maxkp < 1) { snprintf(g_err, sizeof(g_err), "bad matcher options"); return CLB_EINVAL; }
+    CLB_CUDA(cudaSetDevice(device));
+    clb_matcher* m = new (std::nothrow) clb_matcher();
+    if (!m) return CLB_ENOMEM;
+    m->o = *opts; m->device = device; m->n_map = 0; m->stream = nullptr;
+    cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
+    cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);
+    if (e == cudaSuccess) e = m->t.reserve((size_t)opts->maxkp * 64);
+    if (e != cudaSuccess) { int rc = set_cuda_error(e, "matcher allocation", __FILE__, __LINE__); clb_matcher_destroy(m); return rc; }
+    *out = m;
+    return CLB_OK;
+}
+
+void clb_matcher_destroy(clb_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    m->q.release(); m->t.release(); m->map.release(); m->scratch.release(); m->out.release();
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+static int check_sets(clb_matcher* m, const void* Q, int nQ, const void* T, int nT) {
+    if (!m || nQ < 0 || nT < 0 || (nQ > 0 && !Q) || (nT > 0 && !T)) { snprintf(g_err, sizeof(g_err), "bad descriptor set"); return CLB_EINVAL; }
+    return CLB_OK;
+}
+
+int clb_match_2nn(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T, int nT, int threshold,
+                  int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out) {
+    int rc = check_sets(m, Q, nQ, T, nT);
+    if (rc) return rc;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    CLB_CUDA(m->q.reserve((size_t)nQ * 64));
+    CLB_CUDA(m->t.reserve((size_t)(nT > 0 ? nT : 1) * 64));
+    CLB_CUDA(cudaMemcpyAsync(m->q.p, Q, (size_t)nQ * 64, cudaMemcpyHostToDevice, s));
+    if (nT > 0) CLB_CUDA(cudaMemcpyAsync(m->t.p, T, (size_t)nT * 64, cudaMemcpyHostToDevice, s));
+    return run_host(m, m->q.as<uint64_t>(), nQ, m->t.as<uint64_t>(), nT, threshold, 0.f, match_out, best_d_out, second_d_out);
+}
+
+int clb_match_2nn_ratio(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T, int nT, float ratio,
+                        int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out) {
+    int rc = check_sets(m, Q, nQ, T, nT);
+    if (rc) return rc;
+    if (!(ratio > 0.f)) return CLB_EINVAL;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    CLB_CUDA(m->q.reserve((size_t)nQ * 64));
+    CLB_CUDA(m->t.reserve((size_t)(nT > 0 ? nT : 1) * 64));
+    CLB_CUDA(cudaMemcpyAsync(m->q.p, Q, (size_t)nQ * 64, cudaMemcpyHostToDevice, s));
+    if (nT > 0) CLB_CUDA(cudaMemcpyAsync(m->t.p, T, (size_t)nT * 64, cudaMemcpyHostToDevice, s));
+    return run_host(m, m->q.as<uint64_t>(), nQ, m->t.as<uint64_t>(), nT, 0, ratio, match_out, best_d_out, second_d_out);
+}
+
+int clb_match_2nn_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
+                      int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream) {
+    int rc = check_sets(m, dQ, nQ, dT, nT);
+    if (rc) return rc;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    rc = ensure(m, nQ, nT);
+    if (rc) return rc;
+    return launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, 0.f,
+                        d_match_out, d_best_out, d_second_out, nullptr, stream ? (cudaStream_t)stream : m->stream);
+}
+
+int clb_set_map(clb_matcher* m, const uint64_t* M, int nM) {
+    if (!m || nM < 0 || (nM > 0 && !M)) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(m->device));
+    CLB_CUDA(m->map.reserve((size_t)(nM > 0 ? nM : 1) * 64));
+    if (nM > 0) CLB_CUDA(cudaMemcpyAsync(m->map.p, M, (size_t)nM * 64, cudaMemcpyHostToDevice, m->stream));
+    CLB_CUDA(cudaStreamSynchronize(m->stream));
+    m->n_map = nM;
+    return CLB_OK;
+}
+
+int clb_match_map(clb_matcher* m, const uint64_t* Q, int nQ, int threshold,
+                  int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out) {
+    if (!m || nQ < 0 || (nQ > 0 && !Q)) return CLB_EINVAL;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    CLB_CUDA(m->q.reserve((size_t)nQ * 64));
+    CLB_CUDA(cudaMemcpyAsync(m->q.p, Q, (size_t)nQ * 64, cudaMemcpyHostToDevice, m->stream));
+    return run_host(m, m->q.as<uint64_t>(), nQ, m->map.as<uint64_t>(), m->n_map, threshold < 0 ? m->o.thresh : threshold, 0.f,
+                    match_out, best_d_out, second_d_out);
+}
+
+int clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT,
+                          int64_t t_base, clb_partial* d_partial_out, void* stream) {
+    int rc = check_sets(m, dQ, nQ, dT, nT);
+    if (rc) return rc;
+    if (!d_partial_out && nQ > 0) return CLB_EINVAL;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    rc = ensure(m, nQ, nT);
+    if (rc) return rc;
+    return launch_match(dQ, nQ, dT, nT, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
+                        nullptr, nullptr, nullptr, d_partial_out, stream ? (cudaStream_t)stream : m->stream);
+}
+
+int clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,
+                           int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream) {
+    if (!m || nparts < 0 || nQ < 0 || (nQ > 0 && nparts > 0 && !d_parts)) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(m->device));
+    return launch_merge_partials(d_parts, nparts, nQ, threshold, d_match_out, d_best_out, d_second_out,
+                                 stream ? (cudaStream_t)stream : m->stream);
+}
+
+}  // extern "C"

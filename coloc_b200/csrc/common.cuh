@@ -1,0 +1,106 @@
+// common.cuh -- shared device/host helpers for libcoloc_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+#include "../../include/coloc_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libcoloc_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace clb {
+
+extern thread_local char g_err[512];
+extern std::atomic<int64_t> g_launches;
+extern int g_timing;
+
+int set_cuda_error(cudaError_t e, const char* what, const char* file, int line);
+
+#define CLB_CUDA(call)                                                                         \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) return ::clb::set_cuda_error(e__, #call, __FILE__, __LINE__);  \
+    } while (0)
+
+#define CLB_LAUNCHED()                                                                         \
+    do {                                                                                       \
+        ::clb::g_launches.fetch_add(1, std::memory_order_relaxed);                             \
+        cudaError_t e__ = cudaGetLastError();                                                  \
+        if (e__ != cudaSuccess) return ::clb::set_cuda_error(e__, "kernel launch", __FILE__, __LINE__); \
+    } while (0)
+
+// optional per-kernel timing with events on the launching stream (bench's roofline leg)
+struct KernelTimer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    float last_ms = 0.f;
+    bool pending = false;
+    void begin(cudaStream_t s) {
+        if (!g_timing) return;
+        if (!a) { cudaEventCreate(&a); cudaEventCreate(&b); }
+        cudaEventRecord(a, s);
+    }
+    void end(cudaStream_t s) {
+        if (!g_timing) return;
+        cudaEventRecord(b, s); pending = true;
+    }
+    float ms() {
+        if (pending) { cudaEventSynchronize(b); cudaEventElapsedTime(&last_ms, a, b); pending = false; }
+        return last_ms;
+    }
+};
+KernelTimer& timer(const char* which);
+
+// a growable device buffer
+struct DevBuf {
+    void* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace clb
+
+// ---- stage launchers (defined in the .cu files) --------------------------------------------------
+namespace clb {
+
+struct LevelTable {            // passed by value to kernels (fits in param space)
+    int n;
+    int w[CLB_MAX_LEVELS], h[CLB_MAX_LEVELS], stride[CLB_MAX_LEVELS];
+    float f[CLB_MAX_LEVELS];
+    const uint8_t* img[CLB_MAX_LEVELS];
+};
+
+// match.cu
+size_t match_scratch_bytes(int nQ, int nT);
+int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t t_base,
+                 void* scratch, size_t scratch_bytes, int sm_count,
+                 int threshold, float ratio, int32_t* d_match, int32_t* d_best, int32_t* d_second,
+                 clb_partial* d_partial, cudaStream_t s);
+int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int threshold,
+                          int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s);
+// pyramid.cu
+int launch_resize(const LevelTable& lt, cudaStream_t s);   // fills levels 1..n-1 from level 0
+// fast.cu
+struct FastScratch { uint8_t* nms; int* row_count; int* row_off; int* total; };
+size_t fast_scratch_bytes(const LevelTable& lt);
+int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
+                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s);
+// latch.cu
+int launch_describe(const LevelTable& lt, const clb_keypoint* d_kps, int n, const int* d_n, int cap,
+                    uint64_t* d_desc, cudaStream_t s);
+int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t s);
+int latch_init();   // uploads the triplet table
+// microbench.cu
+int microbench_pipes(double* out6);
+
+}  // namespace clb

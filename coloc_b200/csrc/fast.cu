@@ -1,0 +1,296 @@
+// fast.cu -- FAST-9/16 corner score + 3x3 non-max suppression + intensity-centroid orientation,
+// all pyramid levels in one pass, keypoints emitted in the reference's order.
+//
+// Replaces the CPU stage of the reference detector: KFAST<true,true> (include/coloc/KFAST.h:164-540)
+// and featureAngle/fastAtan2 (include/coloc/FeatureAngle.h:160-247) as called per level by
+// GPUDetector.hpp:262-276 -- and with them the 7 D2H pyramid copies + the H2D keypoint copy that
+// bracket that stage.  Semantics (bit-exact set, scores, order):
+//   corner  : >= 9 contiguous ring pixels all > p+t or all < p-t (strict)        KFAST.h:272-290
+//   scanned : rows 3..h-4, cols 3..w-4                                          KFAST.h:431,451,243
+//   score   : max over the 16 arcs of 9 of max(min(p-x), min(x-p))              KFAST.h:304-374
+//   NMS     : score strictly greater than the 8 neighbours' scores              KFAST.h:484-495
+//   order   : level-major, then row-major (y, then x)                           GPUDetector.hpp:262-276
+//   angle   : fastAtan2(sum dy*I, sum dx*I) over the 37-px disc                 FeatureAngle.h:197-247
+// The `1 << 32` edge at KFAST.h:243 is given its intended meaning (all 32 columns valid).
+//
+// Kernels: (1) score+NMS per 64x16 tile staged in shared memory, NMS'd score map + per-row counts
+// out; (2) one-block exclusive scan of the row counts; (3) warp-per-row ordered compaction that
+// also computes the angle.  Integer work, HBM/L2-bound: pyramid read once, 1 B/px map written.
+#include "common.cuh"
+
+namespace clb {
+
+static constexpr int FT_TW = 64, FT_TH = 16;           // output tile
+static constexpr int FT_SW = FT_TW + 8, FT_SH = FT_TH + 8;   // pixels needed: +-4 (3 ring + 1 NMS)
+static constexpr int FT_SSTRIDE = 80;                  // smem row stride (bytes)
+static constexpr int FT_CW = FT_TW + 2, FT_CH = FT_TH + 2;   // score region: +-1
+static constexpr int FT_CSTRIDE = 68;
+
+int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
+
+struct RowMap {   // global row index <-> (level, y)
+    int n; int row_base[CLB_MAX_LEVELS + 1];
+};
+
+__device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int stride, int t) {
+    const int c = p[0];
+    const int hi = c + t, lo = c - t;
+    // cardinal early-out (KFAST.h:186-235): any 9-arc contains two adjacent compass points
+    const int p9 = p[3 * stride], p5 = p[3], p1 = p[-3 * stride], p13 = p[-3];
+    const bool b = ((p9 > hi) & (p5 > hi)) | ((p5 > hi) & (p1 > hi)) | ((p1 > hi) & (p13 > hi)) | ((p13 > hi) & (p9 > hi));
+    const bool d = ((p9 < lo) & (p5 < lo)) | ((p5 < lo) & (p1 < lo)) | ((p1 < lo) & (p13 < lo)) | ((p13 < lo) & (p9 < lo));
+    if (!(b | d)) return 0;
+    int ring[16];
+    ring[0] = p9;                 ring[1] = p[3 * stride + 1];  ring[2] = p[2 * stride + 2];  ring[3] = p[stride + 3];
+    ring[4] = p5;                 ring[5] = p[-stride + 3];     ring[6] = p[-2 * stride + 2]; ring[7] = p[-3 * stride + 1];
+    ring[8] = p1;                 ring[9] = p[-3 * stride - 1]; ring[10] = p[-2 * stride - 2]; ring[11] = p[-stride - 3];
+    ring[12] = p13;               ring[13] = p[stride - 3];     ring[14] = p[2 * stride - 2]; ring[15] = p[3 * stride - 1];
+    uint32_t mb = 0, md = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { mb |= (uint32_t)(ring[k] > hi) << k; md |= (uint32_t)(ring[k] < lo) << k; }
+    // 9 contiguous set bits in the circular 16-bit mask
+    auto run9 = [](uint32_t m) {
+        m |= m << 16;
+        uint32_t a = m & (m >> 1);
+        a &= a >> 2;
+        a &= a >> 4;
+        a &= m >> 8;
+        return (a & 0xFFFFu) != 0;
+    };
+    if (!(run9(mb) | run9(md))) return 0;
+    // score = max over the 16 arcs of 9 of max(min_k(c - x_k), min_k(x_k - c))
+    //       = max(c - min_arcs(max_k x_k), max_arcs(min_k x_k) - c).
+    // Sliding max/min of width 9 on the raw ring values (all in [0,255], non-negative: ptxas 12.9
+    // mis-packs *signed* 32-bit min/max chains into VIMNMX3.U16x2 at -O1+):
+    // width 8 by three doubling steps, then one more element.
+    int mn1[16], mx1[16], mn2[16], mx2[16], mn4[16], mx4[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { mn1[k] = min(ring[k], ring[(k + 1) & 15]); mx1[k] = max(ring[k], ring[(k + 1) & 15]); }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { mn2[k] = min(mn1[k], mn1[(k + 2) & 15]); mx2[k] = max(mx1[k], mx1[(k + 2) & 15]); }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 4) & 15]); mx4[k] = max(mx2[k], mx2[(k + 4) & 15]); }
+    int lo_of_max = 255, hi_of_min = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        lo_of_max = min(lo_of_max, max(mx4[k], ring[(k + 8) & 15]));
+        hi_of_min = max(hi_of_min, min(mn4[k], ring[(k + 8) & 15]));
+    }
+    const int dark = c - lo_of_max, bright = hi_of_min - c;
+    const int best = dark > bright ? dark : bright;
+    return best & 0xFF;
+}
+
+__global__ void __launch_bounds__(256)
+fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
+                int do_nms, int* __restrict__ row_count) {
+    __shared__ __align__(16) uint8_t px[FT_SH * FT_SSTRIDE];
+    __shared__ uint8_t sc[FT_CH * FT_CSTRIDE];
+
+    int tile = blockIdx.x, L = 0, tx_n = 0;
+    for (; L < lt.n; ++L) {
+        tx_n = (lt.w[L] + FT_TW - 1) / FT_TW;
+        const int cnt = tx_n * ((lt.h[L] + FT_TH - 1) / FT_TH);
+        if (tile < cnt) break;
+        tile -= cnt;
+    }
+    if (L >= lt.n) return;
+    const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
+    const uint8_t* __restrict__ img = lt.img[L];
+    const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * FT_TH;
+    const int tid = threadIdx.x;
+
+    // stage (TW+8) x (TH+8) pixels, clamped at the image border (border values are never scored)
+    for (int i = tid; i < FT_SH * (FT_SW / 4); i += 256) {
+        const int r = i / (FT_SW / 4), cq = i % (FT_SW / 4);
+        const int gy = min(max(y0 - 4 + r, 0), h - 1);
+        const int gx = x0 - 4 + cq * 4;
+        const uint8_t* row = img + (size_t)gy * stride;
+        uint32_t v;
+        if (gx >= 0 && gx + 3 < w && ((((uintptr_t)(row + gx)) & 3) == 0)) {
+            v = __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+        } else {
+            v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) v |= (uint32_t)__ldg(row + min(max(gx + k, 0), w - 1)) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(&px[r * FT_SSTRIDE + cq * 4]) = v;
+    }
+    __syncthreads();
+
+    // scores on the (TW+2) x (TH+2) region
+    for (int i = tid; i < FT_CH * FT_CW; i += 256) {
+        const int r = i / FT_CW, c = i % FT_CW;
+        const int gx = x0 - 1 + c, gy = y0 - 1 + r;
+        int s = 0;
+        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3)
+            s = fast_score_px(&px[(r + 3) * FT_SSTRIDE + (c + 3)], FT_SSTRIDE, thresh);
+        sc[r * FT_CSTRIDE + c] = (uint8_t)s;
+    }
+    __syncthreads();
+
+    // NMS + write the map; per-row counts via ballot (each warp covers 32 px of one tile row)
+    uint8_t* map = nms_map;   // per-level maps are addressed through the row map (stride = level stride)
+    const int grow0 = rm.row_base[L];
+#pragma unroll
+    for (int k = 0; k < (FT_TW * FT_TH) / 256; ++k) {
+        const int i = k * 256 + tid;
+        const int r = i / FT_TW, c = i % FT_TW;
+        const int gx = x0 + c, gy = y0 + r;
+        const uint8_t* s1 = &sc[(r + 1) * FT_CSTRIDE + (c + 1)];
+        const int s = s1[0];
+        bool keep = false;
+        if (s && !do_nms) keep = true;
+        else if (s) {
+            keep = (s > s1[-1]) & (s > s1[1]) &
+                   (s > s1[-FT_CSTRIDE - 1]) & (s > s1[-FT_CSTRIDE]) & (s > s1[-FT_CSTRIDE + 1]) &
+                   (s > s1[FT_CSTRIDE - 1]) & (s > s1[FT_CSTRIDE]) & (s > s1[FT_CSTRIDE + 1]);
+        }
+        const bool inside = gx < w && gy < h;
+        keep = keep && inside;
+        if (inside) map[(size_t)(grow0 + gy) * lt.stride[0] + gx] = keep ? (uint8_t)s : (uint8_t)0;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+        if ((tid & 31) == 0 && bal) atomicAdd(&row_count[grow0 + gy], __popc(bal));
+    }
+}
+
+// exclusive scan of row counts (one block); also writes the total
+__global__ void __launch_bounds__(1024)
+row_scan_kernel(const int* __restrict__ row_count, int nrows, int* __restrict__ row_off, int* __restrict__ total) {
+    __shared__ int warp_sum[32];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nrows; base += 1024) {
+        const int i = base + tid;
+        const int v = i < nrows ? row_count[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xFFFFFFFFu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_sum[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            int s = warp_sum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xFFFFFFFFu, s, o); if (lane >= o) s += y; }
+            warp_sum[lane] = s;
+        }
+        __syncthreads();
+        const int prefix = carry + (wid ? warp_sum[wid - 1] : 0) + x - v;
+        if (i < nrows) row_off[i] = prefix;
+        __syncthreads();
+        if (tid == 1023) carry = prefix + v;
+        __syncthreads();
+    }
+    if (tid == 0) *total = carry;
+}
+
+// FeatureAngle.h:160-177 with GCC's -O3 contraction written out (oracle-checked exhaustively)
+__device__ __forceinline__ float fast_atan2_ref(float y, float x) {
+    const float PI = 3.1415927f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, 1.17549435e-38f));
+        const float cc = __fmul_rn(c, c);
+        a = __fmul_rn(__fmaf_rn(__fmaf_rn(__fmaf_rn(-0.0443265555479f, cc, 0.1555786518f), cc, -0.325808397f), cc, 0.9997878412f), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, 1.17549435e-38f));
+        const float cc = __fmul_rn(c, c);
+        const float p = __fmaf_rn(__fmaf_rn(__fmaf_rn(-0.0443265555479f, cc, 0.1555786518f), cc, -0.325808397f), cc, 0.9997878412f);
+        a = __fmaf_rn(-p, c, 1.57079635f);
+    }
+    if (x < 0.0f) a = __fsub_rn(PI, a);
+    if (y < 0.0f) a = -a;
+    return a;
+}
+
+__device__ __forceinline__ float feature_angle(const uint8_t* __restrict__ img, int x, int y, int stride) {
+    int xs = 0, ys = 0;
+#pragma unroll
+    for (int dy = -3; dy <= 3; ++dy) {
+        const int hw = (dy == -3 || dy == 3) ? 1 : ((dy == -2 || dy == 2) ? 2 : 3);
+        const uint8_t* r = img + (size_t)(y + dy) * stride + x;
+#pragma unroll
+        for (int dx = -3; dx <= 3; ++dx) {
+            if (dx < -hw || dx > hw) continue;
+            const int v = __ldg(r + dx);
+            xs += dx * v; ys += dy * v;
+        }
+    }
+    return fast_atan2_ref((float)ys, (float)xs);
+}
+
+// one warp per global row: ordered compaction + angle
+__global__ void __launch_bounds__(256)
+compact_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__ nms_map,
+               const int* __restrict__ row_count, const int* __restrict__ row_off,
+               clb_keypoint* __restrict__ kps, int cap) {
+    const int grow = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (grow >= rm.row_base[rm.n]) return;
+    if (row_count[grow] == 0) return;
+    int L = 0;
+    while (L + 1 < rm.n && grow >= rm.row_base[L + 1]) ++L;
+    const int y = grow - rm.row_base[L];
+    const int w = lt.w[L];
+    const uint8_t* row = nms_map + (size_t)grow * lt.stride[0];
+    int out = row_off[grow];
+    for (int xb = 0; xb < w; xb += 32) {
+        const int x = xb + lane;
+        const int s = x < w ? row[x] : 0;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, s != 0);
+        if (s) {
+            const int pos = out + __popc(bal & ((1u << lane) - 1));
+            if (pos < cap) {
+                clb_keypoint k;
+                k.x = x; k.y = y; k.score = (uint8_t)s; k._pad0[0] = k._pad0[1] = k._pad0[2] = 0;
+                k.angle = feature_angle(lt.img[L], x, y, lt.stride[L]);
+                k.scale = (uint8_t)L; k._pad1[0] = k._pad1[1] = k._pad1[2] = 0;
+                kps[pos] = k;
+            }
+        }
+        out += __popc(bal);
+    }
+}
+
+static RowMap make_rowmap(const LevelTable& lt) {
+    RowMap rm; rm.n = lt.n; rm.row_base[0] = 0;
+    for (int i = 0; i < lt.n; ++i) rm.row_base[i + 1] = rm.row_base[i] + lt.h[i];
+    return rm;
+}
+
+// scratch layout: [nms map: total_rows x stride0][row_count: total_rows ints][row_off: total_rows ints]
+size_t fast_scratch_bytes(const LevelTable& lt) {
+    size_t rows = 0;
+    for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
+    size_t map = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
+    return map + 2 * ((rows * sizeof(int) + 255) & ~(size_t)255) + 256;
+}
+
+int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
+                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s) {
+    if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
+    const RowMap rm = make_rowmap(lt);
+    const size_t rows = rm.row_base[lt.n];
+    const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
+    const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
+    uint8_t* nms = reinterpret_cast<uint8_t*>(scratch);
+    int* row_count = reinterpret_cast<int*>(nms + map_bytes);
+    int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes);
+    CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes, s));
+    int tiles = 0;
+    for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
+    timer("fast").begin(s);
+    fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+    CLB_LAUNCHED();
+    row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);
+    CLB_LAUNCHED();
+    compact_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, row_off, d_kps, cap);
+    timer("fast").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+}  // namespace clb

@@ -1,0 +1,81 @@
+// pyramid.cu -- image pyramid: every level i >= 1 is a bilinear down-scale of LEVEL 0.
+//
+// Replaces CUDALERP (reference src/CUDALERP.cu:153-183) as driven by GPUDetector.hpp:249-255:
+// 7 launches on 7 streams + a zero-fill each become ONE launch covering all levels.  The float
+// expression tree is the one nvcc emits for the reference kernel (PTX-checked):
+//   fx = fma(x+.5, f, -.5); wt = fx - floor(fx); xa = fma(1-wtx, p00, wtx*p10); ...
+//   res = fma(fma(1-wty, xa, wty*xb), 255, .5); store (uint8) truncation
+// with texels read as p/255.f (cudaReadModeNormalizedFloat) and clamp-to-edge addressing.
+#include "common.cuh"
+
+namespace clb {
+
+static constexpr int RZ_TX = 32, RZ_TY = 8, RZ_PX = 4;     // thread block 32x8, 4 px per thread
+static constexpr int RZ_TILE_W = RZ_TX * RZ_PX;            // 128 x 8 output pixels per CTA
+
+__device__ __forceinline__ float unorm8(uint8_t v) { return __fdiv_rn((float)v, 255.0f); }
+
+__global__ void __launch_bounds__(RZ_TX * RZ_TY)
+resize_levels_kernel(const LevelTable lt) {
+    // which level / tile does this CTA own?
+    int tile = blockIdx.x, L = 1, tx_n = 0;
+    for (; L < lt.n; ++L) {
+        tx_n = (lt.w[L] + RZ_TILE_W - 1) / RZ_TILE_W;
+        const int cnt = tx_n * ((lt.h[L] + RZ_TY - 1) / RZ_TY);
+        if (tile < cnt) break;
+        tile -= cnt;
+    }
+    if (L >= lt.n) return;
+    const int w0 = lt.w[0], h0 = lt.h[0], s0 = lt.stride[0];
+    const uint8_t* __restrict__ src = lt.img[0];
+    uint8_t* __restrict__ dst = const_cast<uint8_t*>(lt.img[L]);
+    const int dw = lt.w[L], dh = lt.h[L], ds = lt.stride[L];
+    const float f = lt.f[L];
+
+    const int y = (tile / tx_n) * RZ_TY + threadIdx.y;
+    const int xb = (tile % tx_n) * RZ_TILE_W + threadIdx.x * RZ_PX;
+    if (y >= dh || xb >= dw) return;
+
+    const float fy = __fmaf_rn((float)(uint32_t)y + 0.5f, f, -0.5f);
+    const float fly = floorf(fy);
+    const float wty = __fsub_rn(fy, fly), ivy = __fsub_rn(1.0f, wty);
+    const int y0 = min(max((int)fly, 0), h0 - 1), y1 = min(max((int)fly + 1, 0), h0 - 1);
+    const uint8_t* r0 = src + (size_t)y0 * s0;
+    const uint8_t* r1 = src + (size_t)y1 * s0;
+
+    uint32_t packed = 0;
+#pragma unroll
+    for (int k = 0; k < RZ_PX; ++k) {
+        const int x = xb + k;
+        const float fx = __fmaf_rn((float)(uint32_t)x + 0.5f, f, -0.5f);
+        const float flx = floorf(fx);
+        const float wtx = __fsub_rn(fx, flx), ivx = __fsub_rn(1.0f, wtx);
+        const int x0 = min(max((int)flx, 0), w0 - 1), x1 = min(max((int)flx + 1, 0), w0 - 1);
+        const float p00 = unorm8(__ldg(r0 + x0)), p10 = unorm8(__ldg(r0 + x1));
+        const float p01 = unorm8(__ldg(r1 + x0)), p11 = unorm8(__ldg(r1 + x1));
+        const float xa = __fmaf_rn(ivx, p00, __fmul_rn(wtx, p10));
+        const float xbv = __fmaf_rn(ivx, p01, __fmul_rn(wtx, p11));
+        const float res = __fmaf_rn(__fmaf_rn(ivy, xa, __fmul_rn(wty, xbv)), 255.0f, 0.5f);
+        packed |= (__float2uint_rz(res) & 0xFFu) << (8 * k);
+    }
+    uint8_t* o = dst + (size_t)y * ds + xb;
+    if (xb + RZ_PX <= dw && (((uintptr_t)o) & 3) == 0) {
+        *reinterpret_cast<uint32_t*>(o) = packed;
+    } else {
+        for (int k = 0; k < RZ_PX && xb + k < dw; ++k) o[k] = (uint8_t)(packed >> (8 * k));
+    }
+}
+
+int launch_resize(const LevelTable& lt, cudaStream_t s) {
+    int tiles = 0;
+    for (int L = 1; L < lt.n; ++L)
+        tiles += ((lt.w[L] + RZ_TILE_W - 1) / RZ_TILE_W) * ((lt.h[L] + RZ_TY - 1) / RZ_TY);
+    if (tiles == 0) return CLB_OK;
+    timer("resize").begin(s);
+    resize_levels_kernel<<<tiles, dim3(RZ_TX, RZ_TY), 0, s>>>(lt);
+    timer("resize").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+}  // namespace clb

@@ -1,0 +1,163 @@
+/* coloc_b200.h -- C ABI of the B200-native CoLoC front end (libcoloc_b200.so).
+ *
+ * Drop-in boundary for the reference's GPU detector / matcher policies.  Every entry point names
+ * the reference interface it replaces (paths relative to the reference repo root).  Plain
+ * pointers and sizes only; no C++/torch types.  All functions return 0 (CLB_OK) or a CLB_E*
+ * code; clb_strerror() explains it and clb_last_error() returns the CUDA detail of the last
+ * failure on the calling thread.
+ *
+ * Host-pointer entry points (suffix-less) have the reference's blocking semantics: they copy
+ * inputs H2D, run, copy results D2H and return after a stream sync (GPUDetector.hpp:290,
+ * CUDAK2NN.cu:80).  `_dev` entry points take DEVICE pointers plus a cudaStream_t (passed as
+ * void*) and only enqueue work.
+ */
+#ifndef COLOC_B200_H
+#define COLOC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CLB_OK            0
+#define CLB_EINVAL        1   /* bad argument */
+#define CLB_ECUDA         2   /* a CUDA runtime call failed (see clb_last_error) */
+#define CLB_ECAPACITY     3   /* caller buffer / maxkp too small; *n_out holds the needed count */
+#define CLB_ENOMEM        4
+#define CLB_EUNSUPPORTED  5
+
+#define CLB_MAX_LEVELS    16
+#define CLB_NO_MATCH      (-1)
+#define CLB_BEST_NONE     100000   /* CUDAK2NN.cu:54 initial best   */
+#define CLB_SECOND_NONE   200000   /* CUDAK2NN.cu:54 initial second */
+
+/* include/coloc/Keypoint.h:155-164 -- same 20-byte layout, copied raw by GPUDetector.hpp:281 */
+typedef struct clb_keypoint {
+    int32_t x, y;            /* level coordinates */
+    uint8_t score; uint8_t _pad0[3];
+    float   angle;           /* (-pi, pi] */
+    uint8_t scale; uint8_t _pad1[3];   /* pyramid level */
+} clb_keypoint;
+
+/* include/coloc/colocData.hpp:29-36 DetectorOptions, field for field */
+typedef struct clb_detector_opts {
+    float    scale_factor;   /* 1.2 in coloc_node.cpp:78 */
+    int32_t  scale_levels;   /* 8 */
+    int32_t  width, height;  /* maximum frame size (buffers are sized for it) */
+    int32_t  maxkp;          /* capacity of the keypoint / descriptor buffers */
+    int32_t  thresh;         /* FAST threshold, 40 in coloc_node.cpp:81 */
+} clb_detector_opts;
+
+/* include/coloc/colocData.hpp:38-42 MatcherOptions */
+typedef struct clb_matcher_opts {
+    float    distRatio;      /* used by the ratio-test mode only (CPUMatcher.hpp:58-89) */
+    int32_t  thresh;         /* absolute margin for map matching, 60 in coloc_node.cpp:85 */
+    int32_t  maxkp;          /* initial capacity in descriptors (grows on demand) */
+} clb_matcher_opts;
+
+typedef struct clb_detector clb_detector;
+typedef struct clb_matcher  clb_matcher;
+
+/* per-query partial 2-NN state exchanged between DB shards (multi-GPU) */
+typedef struct clb_partial {
+    int32_t best_d;     /* CLB_BEST_NONE when the shard was empty */
+    int32_t best_i;     /* GLOBAL row index of the first row attaining best_d, -1 if none */
+    int32_t second_d;   /* second-smallest distance in the shard (== best_d on ties) */
+    int32_t _pad;
+} clb_partial;
+
+const char* clb_strerror(int code);
+const char* clb_last_error(void);
+int  clb_version(void);
+int  clb_device_count(int* n_out);
+
+/* ---------------------------------------------------------------- detector --------------- */
+/* GPUDetector::GPUDetector(DetectorOptions)  include/coloc/GPUDetector.hpp:70-138 */
+int  clb_detector_create(const clb_detector_opts* opts, int device, clb_detector** out);
+/* GPUDetector::freeGPUMemory  GPUDetector.hpp:144-155 */
+void clb_detector_destroy(clb_detector* d);
+
+/* level geometry of GPUDetector.hpp:107-114 for a w x h frame; arrays of scale_levels entries */
+int  clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, int32_t* hs, float* fs);
+
+/* GPUDetector::detectAndDescribe  GPUDetector.hpp:216-291 (everything after cv::imread):
+ * gray (HOST, 8-bit, `stride` bytes per row) -> keypoints in level-major / row-major order
+ * (:262-276) and 8 x uint64 descriptors per keypoint (:282-288).  If the frame has more than
+ * `cap` (or maxkp) keypoints returns CLB_ECAPACITY with *n_out = needed. */
+int  clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int stride,
+                         clb_keypoint* kps_out, uint64_t* desc_out, int cap, int* n_out);
+/* same with a DEVICE image; results stay on the device (d_kps / d_desc owned by the detector,
+ * valid until the next call); *n_out is read back (one 4-byte D2H + stream sync). */
+int  clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h, int stride,
+                             const clb_keypoint** d_kps, const uint64_t** d_desc, int* n_out, void* stream);
+
+/* stage-level entry points (parity tests) */
+/* CUDALERP x (levels-1)  src/CUDALERP.cu:153-183 as driven by GPUDetector.hpp:249-255.
+ * levels_out (HOST): levels packed back to back, level i is ws[i] x hs[i] with stride ws[i];
+ * level 0 is a copy of the input. */
+int  clb_pyramid(clb_detector* d, const uint8_t* gray, int w, int h, int stride, uint8_t* levels_out);
+/* KFAST<true,true> + featureAngle on one level image  include/coloc/KFAST.h:503,
+ * FeatureAngle.h:197; caller GPUDetector.hpp:268-274.  level_idx is stored in kp.scale. */
+int  clb_fast_nms_angle(clb_detector* d, const uint8_t* level, int w, int h, int stride, int level_idx,
+                        clb_keypoint* kps_out, int cap, int* n_out);
+/* CLATCH  src/CLATCH.cu:153-193 on caller-supplied level images (HOST pointers). */
+int  clb_describe(clb_detector* d, const uint8_t* const* levels, const int32_t* ws, const int32_t* hs,
+                  const int32_t* strides, int nlevels, const clb_keypoint* kps, int n, uint64_t* desc_out);
+/* device sin/cos used by the describe kernel (CLATCH.cu:161), for ulp-level parity tests */
+int  clb_sincos(clb_detector* d, const float* angles, int n, float* sin_out, float* cos_out);
+
+/* ---------------------------------------------------------------- matcher ---------------- */
+/* GPUMatcher::GPUMatcher(MatcherOptions)  include/coloc/GPUMatcher.hpp:70-95 */
+int  clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** out);
+/* GPUMatcher::freeGPUMemory  GPUMatcher.hpp:102-108 */
+void clb_matcher_destroy(clb_matcher* m);
+
+/* GPUMatcher::computeMatches(void* hQ, void* hT, int nQ, int nT, uint8_t threshold)
+ * GPUMatcher.hpp:180-226 -> CUDAK2NN  src/CUDAK2NN.cu:42-81.  HOST pointers.
+ * match_out[q] = first T row attaining the minimum distance if second - best > threshold,
+ * else -1.  best_d_out / second_d_out optional (may be NULL). */
+int  clb_match_2nn(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T, int nT, int threshold,
+                   int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
+/* same on DEVICE pointers (16-byte aligned), enqueue only */
+int  clb_match_2nn_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
+                       int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
+/* GPUMatcher::setMapData  GPUMatcher.hpp:110-117 (HOST pointer; H2D once per map) */
+int  clb_set_map(clb_matcher* m, const uint64_t* M, int nM);
+/* GPUMatcher::setQueryImage + matchFeaturesWithMap  GPUMatcher.hpp:130-141,252-271
+ * threshold < 0 -> opts.thresh.  match_out[q] = MAP row or -1 (the caller flips it into
+ * IndMatch(map, frame) as :263-266 does). */
+int  clb_match_map(clb_matcher* m, const uint64_t* Q, int nQ, int threshold,
+                   int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
+
+/* ratio-test mode mirroring the CPU build (CPUMatcher.hpp:67-76 -> matching_filters.hpp:39-60):
+ * keep iff best < ratio * second (float compare).  HOST pointers. */
+int  clb_match_2nn_ratio(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T, int nT, float ratio,
+                         int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
+
+/* DB-row sharding: local 2-NN of every query against DEVICE rows dT[0..nT) whose
+ * global indices start at t_base; d_partial_out[nQ] (device).  Enqueue only. */
+int  clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT,
+                           int64_t t_base, clb_partial* d_partial_out, void* stream);
+/* merge `nparts` partial arrays laid out [part][nQ] (ascending t_base order) and apply the margin
+ * test: first-min-wins across parts, global second = 2nd smallest of the union.  DEVICE pointers. */
+int  clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,
+                            int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
+/* ---------------------------------------------------------------- measurement ------------ */
+/* pipe micro-benchmarks that back the match roofline: dependent-free POPC / LOP3
+ * streams and a mixed stream; results in ops per clock per SM and the SM clock seen.
+ * out[0]=popc/clk/SM out[1]=lop3/clk/SM out[2]=mixed popc/clk/SM out[3]=mixed lop3/clk/SM
+ * out[4]=SM MHz during the run  out[5]=SM count */
+int  clb_microbench_pipes(int device, double* out6);
+/* number of kernels this library launched on the calling process so far (bench's gpu_launches) */
+int64_t clb_launch_count(void);
+/* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */
+int  clb_set_timing(int on);
+/* tuning knobs for experiments: "match_rq" (0,1,2,4), "match_hs" (0..3), "match_chunks" (0 = auto) */
+int  clb_set_param(const char* name, int value);
+float clb_last_kernel_ms(const char* which);   /* "match", "describe", "fast", "resize", "merge" */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

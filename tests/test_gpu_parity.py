@@ -1,0 +1,263 @@
+"""GPU parity tests (the gate): the CUDA path, called through the C ABI, against the CPU oracle on
+identical seeded inputs, against the committed golden fixtures, and -- at BASELINE sizes --
+through size-independent properties.  Integer/byte/index work is compared bit-exactly; the only
+floating-point outputs (angle, pyramid) are also required to be bit-identical to the oracle's
+explicit-fma restatement (tolerance stated per test; north_star allows 1 LSB on pyramid pixels)."""
+import os
+
+import numpy as np
+import pytest
+
+from coloc_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def matcher(clb):
+    m = clb.Matcher(maxkp=4096)
+    yield m
+    m.close()
+
+
+def _check_match(clb, oracle, matcher, Q, T, thr):
+    got = matcher.compute_matches(Q, T, thr, want_dist=True)
+    ref = oracle.match_2nn(Q, T, thr)
+    for name, a, b in zip(("match", "best", "second"), got, ref):
+        assert np.array_equal(a, b), (name, int((a != b).sum()))
+
+
+# ------------------------------------------------------------------ Hamming 2-NN
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (3, 1), (7, 5), (33, 64), (64, 65), (255, 257), (300, 1000),
+                                   (1000, 777), (2049, 4100), (5000, 5000)])
+@pytest.mark.parametrize("hs", [0, 1, 2, 3])
+def test_match_vs_oracle(clb, oracle, matcher, nq, nt, hs):
+    if hs != 2 and nq > 1000:
+        pytest.skip("knob sweep on small sizes only")
+    clb.set_param("match_hs", hs)
+    try:
+        T = synth.random_descriptors(nt, 100 + nt)
+        Q, _ = synth.planted_queries(T, nq, 200 + nq)
+        rng = np.random.default_rng(nq * 7 + nt)
+        k = max(1, nq // 4)
+        Q[:k] = T[rng.integers(0, nt, k)]                    # exact hits
+        if nt > 4:
+            T[nt // 2] = T[1]; T[nt - 1] = T[1]              # duplicated rows -> ties, first index must win
+        for thr in (40, 60, 0):
+            _check_match(clb, oracle, matcher, Q, T, thr)
+    finally:
+        clb.set_param("match_hs", 2)
+
+
+@pytest.mark.parametrize("rq", [1, 2, 4])
+@pytest.mark.parametrize("chunks", [1, 3, 0])
+def test_match_knobs(clb, oracle, matcher, rq, chunks):
+    clb.set_param("match_rq", rq); clb.set_param("match_chunks", chunks)
+    try:
+        T = synth.random_descriptors(1500, 1); Q, _ = synth.planted_queries(T, 700, 2)
+        T[900] = T[10]
+        _check_match(clb, oracle, matcher, Q, T, 40)
+    finally:
+        clb.set_param("match_rq", 0); clb.set_param("match_chunks", 0)
+
+
+def test_match_edge_cases(clb, oracle, matcher):
+    T = synth.random_descriptors(8, 5)
+    # empty DB: no match, sentinels of CUDAK2NN.cu:54
+    m, b, s = matcher.compute_matches(T[:3], T[:0], 40, want_dist=True)
+    assert list(m) == [-1] * 3 and list(b) == [100000] * 3 and list(s) == [200000] * 3
+    # empty query set
+    assert len(matcher.compute_matches(T[:0], T, 40)) == 0
+    # one DB row: always matched
+    m, b, s = matcher.compute_matches(T[:4], T[:1], 40, want_dist=True)
+    assert list(m) == [0] * 4 and list(s) == [100000] * 4 and b[0] == 0
+    # all-zero and all-one rows: distance 512
+    Z = np.zeros((1, 8), np.uint64); F = np.full((2, 8), np.uint64(0xFFFFFFFFFFFFFFFF))
+    m, b, s = matcher.compute_matches(Z, F, 40, want_dist=True)
+    assert b[0] == 512 and s[0] == 512 and m[0] == -1
+    _check_match(clb, oracle, matcher, T, T, 40)             # self match: distance 0 everywhere
+
+
+def test_match_golden(clb, matcher):
+    g = np.load(os.path.join(GOLD, "match_small.npz"))
+    m, b, s = matcher.compute_matches(g["Q"], g["T"], int(g["threshold"]), want_dist=True)
+    assert np.array_equal(m, g["match"]) and np.array_equal(b, g["best"]) and np.array_equal(s, g["second"])
+    # ratio mode reproduces openMVG's NNdistanceRatio decisions (generated from the reference's compiled code)
+    mr = matcher.compute_matches_ratio(g["Q"], g["T"], 0.8)
+    assert np.array_equal(mr >= 0, g["ratio_ok"].astype(bool))
+
+
+def test_match_map_api(clb, oracle, matcher):
+    M = synth.random_descriptors(3000, 9); Q, src = synth.planted_queries(M, 500, 10)
+    matcher.set_map_data(M)
+    got = matcher.match_with_map(Q, want_dist=True)          # threshold from opts (60), GPUMatcher.hpp:256
+    ref = oracle.match_2nn(Q, M, 60)
+    assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+    t = src >= 0
+    assert (got[0][t] == src[t]).mean() > 0.95               # planted matches recovered
+
+
+def test_match_full_size_properties(clb, oracle):
+    """C4-shaped run (50k queries; DB cut to 400k rows to keep the test short): properties that do not need the
+    oracle at full size + an oracle check on a 64-query slice."""
+    nq, nt = 50000, 400000
+    T = synth.random_descriptors(nt, 42); Q, src = synth.planted_queries(T, nq, 43)
+    m = clb.Matcher(maxkp=nt)
+    match, best, second = m.compute_matches(Q, T, 40, want_dist=True)
+    t = src >= 0
+    assert (match[t] == src[t]).mean() > 0.999               # d~51 vs random ~256: all planted rows found
+    assert (match[~t] == -1).mean() > 0.99
+    assert (best <= second).all() and (best[t] < 120).all()
+    # linearity: XOR-ing every row with the same mask leaves all distances unchanged
+    mask = synth.random_descriptors(1, 7)
+    m2, b2, s2 = m.compute_matches(Q[:5000] ^ mask, T ^ mask, 40, want_dist=True)
+    assert np.array_equal(m2, match[:5000]) and np.array_equal(b2, best[:5000]) and np.array_equal(s2, second[:5000])
+    # oracle on a slice
+    sl = slice(1000, 1064)
+    ro = oracle.match_2nn(Q[sl], T, 40)
+    assert np.array_equal(ro[0], match[sl]) and np.array_equal(ro[1], best[sl]) and np.array_equal(ro[2], second[sl])
+    m.close()
+
+
+def test_partial_and_merge(clb, oracle):
+    """DB-row sharding on one GPU: partials of 3 uneven shards + merge == single scan."""
+    import torch
+    nq, nt = 1200, 5000
+    T = synth.random_descriptors(nt, 3); Q, _ = synth.planted_queries(T, nq, 4)
+    T[4000] = T[10]; T[2500] = T[10]                          # ties across shards: lowest global index wins
+    Q[0] = T[10]
+    m = clb.Matcher(maxkp=nt)
+    dQ = torch.from_numpy(Q.view(np.int64)).cuda(); dT = torch.from_numpy(T.view(np.int64)).cuda()
+    bounds = [0, 1700, 1700, 3301, nt]                        # includes an empty shard
+    parts = torch.zeros((len(bounds) - 1, nq, 4), dtype=torch.int32, device="cuda")
+    for i in range(len(bounds) - 1):
+        a, b = bounds[i], bounds[i + 1]
+        m.match_partial_dev(dT.new_tensor([]) if False else dQ, nq, dT[a:] if b > a else dT, b - a, a, parts[i])
+    out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+    m.merge_partials_dev(parts, len(bounds) - 1, nq, 40, out[0], out[1], out[2])
+    torch.cuda.synchronize()
+    ref = oracle.match_2nn(Q, T, 40)
+    got = out.cpu().numpy()
+    for i in range(3):
+        assert np.array_equal(got[i], ref[i]), i
+    m.close()
+
+
+# ------------------------------------------------------------------ pyramid
+@pytest.mark.parametrize("w,h", [(640, 480), (1280, 720), (333, 251), (64, 48)])
+def test_pyramid_vs_oracle(clb, oracle, w, h):
+    img = synth.textured_frame(w, h, 5)
+    det = clb.Detector(w, h, maxkp=1000)
+    got = det.pyramid(img)
+    ref = oracle.pyramid(img)
+    for L, (a, b) in enumerate(zip(got, ref)):
+        assert a.shape == b.shape
+        # north_star tolerance is 1 LSB; the explicit-fma tree is in fact bit-identical
+        assert np.array_equal(a, b), (L, int(np.abs(a.astype(int) - b.astype(int)).max()))
+    det.close()
+
+
+# ------------------------------------------------------------------ FAST + NMS + angle
+@pytest.mark.parametrize("w,h,thr", [(640, 480, 40), (533, 400, 40), (1067, 600, 40), (257, 193, 20), (70, 50, 10),
+                                     (214, 161, 20), (9, 9, 5), (7, 7, 1), (6, 30, 5)])
+def test_fast_vs_oracle(clb, oracle, w, h, thr):
+    img = synth.textured_frame(w, h, 3)
+    det = clb.Detector(max(w, 8), max(h, 8), maxkp=w * h // 4 + 16, thresh=thr)
+    got = det.fast_nms_angle(img, level_idx=2)
+    ref = oracle.fast_nms(img, thr, quirk=0)
+    for k in ref:
+        k["angle"] = oracle.feature_angle(img, k["x"], k["y"]); k["scale"] = 2
+    assert len(got) == len(ref)
+    assert np.array_equal(got.view(np.uint8), ref.view(np.uint8))   # x, y, score, angle bits, scale, order
+    det.close()
+
+
+def test_fast_noise_and_flat(clb, oracle):
+    det = clb.Detector(640, 480, maxkp=200000, thresh=40)
+    noise = np.random.default_rng(0).integers(0, 256, (480, 640), dtype=np.uint8)
+    got = det.fast_nms_angle(noise)
+    ref = oracle.fast_nms(noise, 40)
+    assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
+    assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
+    det.close()
+
+
+def test_fast_capacity_error(clb):
+    det = clb.Detector(640, 480, maxkp=100, thresh=40)
+    noise = np.random.default_rng(0).integers(0, 256, (480, 640), dtype=np.uint8)
+    with pytest.raises(clb.ClbError) as e:
+        det.fast_nms_angle(noise)
+    assert e.value.code == 3
+    det.close()
+
+
+# ------------------------------------------------------------------ LATCH describe
+def test_sincos_bit_exact(clb, oracle):
+    det = clb.Detector(64, 64, maxkp=16)
+    a = np.concatenate([np.linspace(-np.pi, np.pi, 400001), [0.0, np.pi, -np.pi, 1e-8, -1e-8]]).astype(np.float32)
+    s, c = det.sincos(a)
+    so, co = oracle.sincos_many(a)
+    assert np.array_equal(s.view(np.uint32), so.view(np.uint32)) and np.array_equal(c.view(np.uint32), co.view(np.uint32))
+    det.close()
+
+
+@pytest.mark.parametrize("w,h", [(640, 480), (320, 240)])
+def test_describe_vs_oracle(clb, oracle, w, h):
+    img = synth.textured_frame(w, h, 8)
+    pyr = oracle.pyramid(img)
+    kps, _ = oracle.detect_describe(img, thresh=30, cap=50000)
+    # add border keypoints (clamp-to-edge sampling) and arbitrary angles
+    extra = np.zeros(6, kps.dtype)
+    extra["x"] = [0, w - 1, 3, w - 4, 10, 5]; extra["y"] = [0, h - 1, 3, h - 4, 2, h - 2]
+    extra["angle"] = [0.0, 3.1415927, -3.1415927, 0.7853982, -1.5707964, 2.5]
+    kps = np.concatenate([kps, extra])
+    det = clb.Detector(w, h, maxkp=len(kps) + 1)
+    got = det.describe(pyr, kps)
+    ref = oracle.latch_describe(pyr, kps)
+    bad = (got != ref).any(axis=1)
+    assert not bad.any(), (int(bad.sum()), len(kps))
+    det.close()
+
+
+# ------------------------------------------------------------------ whole frame
+@pytest.mark.parametrize("w,h", [(640, 480), (1280, 720)])
+def test_detect_describe_end_to_end(clb, oracle, w, h):
+    a, b, H = synth.frame_pair(w, h, 0)
+    det = clb.Detector(w, h, maxkp=100000)
+    for img in (a, b):
+        kps, desc = det.detect_and_describe(img)
+        okps, odesc = oracle.detect_describe(img, cap=100000)
+        assert len(kps) == len(okps) > 1000
+        assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8))
+        assert np.array_equal(desc, odesc)
+    det.close()
+
+
+def test_golden_frame(clb):
+    g = np.load(os.path.join(GOLD, "frame168.npz"))
+    det = clb.Detector(168, 126, maxkp=5000, thresh=int(g["thresh"]))
+    kps, desc = det.detect_and_describe(g["img"])
+    assert np.array_equal(kps.view(np.uint8), g["kps"].view(np.uint8)) and np.array_equal(desc, g["desc"])
+    det.close()
+
+
+def test_pair_pipeline_recovers_homography(clb, oracle):
+    """C1-shaped: detect+describe both views, 2-NN match (margin 40), matches agree with the known homography."""
+    w, h = 640, 480
+    a, b, H = synth.frame_pair(w, h, 1)
+    det = clb.Detector(w, h, maxkp=50000)
+    ka, da = det.detect_and_describe(a); ka, da = ka.copy(), da.copy()
+    kb, db = det.detect_and_describe(b)
+    m = clb.Matcher(maxkp=50000)
+    match = m.compute_matches(da, db, 40)
+    assert np.array_equal(match, oracle.match_2nn(da, db, 40)[0])
+    idx = np.nonzero(match >= 0)[0]
+    assert len(idx) > 50
+    sa = np.float32(1.2) ** ka["scale"][idx]; sb = np.float32(1.2) ** kb["scale"][match[idx]]
+    pa = np.stack([ka["x"][idx] * sa, ka["y"][idx] * sa, np.ones(len(idx))])
+    pb = H @ pa; pb = pb[:2] / pb[2]
+    err = np.hypot(pb[0] - kb["x"][match[idx]] * sb, pb[1] - kb["y"][match[idx]] * sb)
+    assert np.median(err) < 3.0 and (err < 6).mean() > 0.8
+    det.close(); m.close()

@@ -1,0 +1,42 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/*.npz.  Run in the build container (where /root/reference exists): the
+keypoints come from the REFERENCE's compiled KFAST.h + FeatureAngle.h (oracle/_ref) and are asserted
+equal to the restatement before being written; descriptors / pyramid / matches come from the
+restatement (the reference's CUDA kernels cannot run here: no GPU).  The fixtures then pin the
+oracle on machines without /root/reference, and the CUDA path through tests/test_gpu_parity.py."""
+import hashlib, os, sys
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import oracle as O
+from coloc_b200 import synth
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+os.makedirs(GOLD, exist_ok=True)
+assert O.ref_cpu() is not None, "build oracle/_ref first (make -C oracle ref_cpu)"
+
+img = synth.textured_frame(168, 126, 77)
+thresh = 20
+kps, desc, pyr = O.detect_describe(img, thresh=thresh, want_pyramid=True)
+# cross-check every level's keypoints + angles against the reference's compiled CPU code
+off = 0
+for L, lv in enumerate(pyr):
+    ref = O.ref_kfast(lv, thresh)
+    mine = kps[kps["scale"] == L]
+    assert len(ref) == len(mine) and np.array_equal(ref["x"], mine["x"]) and np.array_equal(ref["y"], mine["y"]) \
+        and np.array_equal(ref["score"], mine["score"]), L
+    for k in mine:
+        assert np.float32(O.ref_feature_angle(lv, k["x"], k["y"])).view(np.uint32) == k["angle"].view(np.uint32)
+np.savez_compressed(os.path.join(GOLD, "frame168.npz"), img=img, thresh=thresh, kps=kps, desc=desc,
+                    pyr_sha256=hashlib.sha256(b"".join(p.tobytes() for p in pyr)).hexdigest())
+print("frame168:", len(kps), "keypoints")
+
+T = synth.random_descriptors(257, 21)
+Q, src = synth.planted_queries(T, 96, 22)
+Q[:8] = T[:8]; T[100] = T[3]          # exact hits + a duplicated row (tie on best)
+m, b, s = O.match_2nn(Q, T, 40)
+idx, dist, ok = O.ref_bruteforce_2nn(T, Q, 0.8)
+assert np.array_equal(dist[:, 0], b) and np.array_equal(dist[:, 1], s)
+np.savez_compressed(os.path.join(GOLD, "match_small.npz"), Q=Q, T=T, threshold=40, match=m, best=b, second=s,
+                    ratio_ok=ok)
+print("match_small:", int((m >= 0).sum()), "matches of", len(Q))
