@@ -134,7 +134,7 @@ def test_partial_and_merge(clb, oracle):
     parts = torch.zeros((len(bounds) - 1, nq, 4), dtype=torch.int32, device="cuda")
     for i in range(len(bounds) - 1):
         a, b = bounds[i], bounds[i + 1]
-        m.match_partial_dev(dT.new_tensor([]) if False else dQ, nq, dT[a:] if b > a else dT, b - a, a, parts[i])
+        m.match_partial_dev(dQ, nq, dT[a:] if b > a else dT, b - a, a, parts[i])
     out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
     m.merge_partials_dev(parts, len(bounds) - 1, nq, 40, out[0], out[1], out[2])
     torch.cuda.synchronize()
