@@ -1,0 +1,351 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the CoLoC front-end hot path on B200.
+
+Metric (BASELINE.json): Hamming 512-bit comparisons/s, on BASELINE config 4 ("map relocalization:
+50k query descriptors vs 2M-descriptor synthetic map database, database rows sharded over N GPUs"),
+the largest matching configuration and the one the reference's only published number (63e9 cmp/s on
+a GTX 1080, src/CUDAK2NN.cu:24) is a like-for-like of.  A step = one full 2-NN match of all queries
+against the whole DB.  N > 1: DB rows are sharded over the ranks (strong scaling, total work fixed),
+one all-gather of per-query partials + a device merge per step.
+
+  value : whole-job comparisons/s, inputs resident in HBM (per-step CUDA events, max over ranks)
+  e2e   : same metric through the host-buffer API (pinned host Q and this rank's T rows copied H2D
+          and match[] copied D2H inside the timed region, every step)
+  extra : keypoint frames/s and per-stage numbers for config 2 (1280x720 pair, detect+describe+match)
+
+`--impl reference` times the reference's own CPU matcher (openMVG ArrayMatcherBruteForce<uchar,Hamming>
++ NNdistanceRatio, compiled from /root/reference into oracle/_ref) on a bounded query sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NQ, NT, THRESH = 50000, 2000000, 60       # config 4; threshold = opts.thresh of coloc_node.cpp:85
+PUBLISHED_CMP_S = 63e9                    # BASELINE.md section 1 (GTX 1080)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_db_shard(lo, hi):
+    """rows [lo, hi) of the seed-42 DB, generated blockwise so every rank builds only its shard."""
+    blk = 250000
+    out = np.empty((hi - lo, 8), np.uint64)
+    for b0 in range((lo // blk) * blk, hi, blk):
+        rows = np.random.default_rng([42, b0 // blk]).integers(0, 2 ** 64, size=(blk, 8), dtype=np.uint64)
+        a, b = max(lo, b0), min(hi, b0 + blk)
+        out[a - lo:b - lo] = rows[a - b0:b - b0]
+    return out
+
+
+def make_queries(nq, nt):
+    """80 % = DB rows with each bit flipped w.p. 0.10 (true matches), 20 % fresh random rows; seed 43."""
+    rng = np.random.default_rng(43)
+    n_true = int(nq * 0.8)
+    src = np.full(nq, -1, np.int64); src[:n_true] = rng.integers(0, nt, n_true)
+    Q = rng.integers(0, 2 ** 64, size=(nq, 8), dtype=np.uint64)
+    blk = 250000
+    for b in np.unique(src[:n_true] // blk):
+        rows = np.random.default_rng([42, int(b)]).integers(0, 2 ** 64, size=(blk, 8), dtype=np.uint64)
+        sel = np.nonzero(src[:n_true] // blk == b)[0]
+        Q[sel] = rows[src[sel] - b * blk]
+    bits = rng.random((n_true, 8, 64), dtype=np.float32) < 0.10
+    Q[:n_true] ^= (bits.astype(np.uint64) << np.arange(64, dtype=np.uint64)).sum(axis=2, dtype=np.uint64)
+    perm = rng.permutation(nq)
+    return Q[perm], src[perm]
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    """reference arm: the reference's CPU matcher on the box's host cores, bounded sample per step."""
+    if rank != 0:
+        return
+    import oracle as O
+    kind = "reference" if O.ref_cpu() is not None else "port"
+    cores = os.cpu_count()
+    nt = NT
+    T = make_db_shard(0, nt)
+    Q, _ = make_queries(NQ, nt)
+    # size the sample so one step is ~2 s: probe with 32 queries
+    t0 = time.perf_counter()
+    (O.ref_bruteforce_2nn(T, Q[:32], 0.8) if kind == "reference" else O.match_2nn(Q[:32], T, THRESH))
+    per_q = (time.perf_counter() - t0) / 32
+    nq_s = int(min(NQ, max(64, 2.0 / per_q)))
+    Qs = Q[:nq_s]
+    times = []
+    for it in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        if kind == "reference":
+            O.ref_bruteforce_2nn(T, Qs, 0.8)
+        else:
+            O.match_2nn(Qs, T, THRESH)
+        if it >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    tot = sum(times)
+    v = nq_s * nt * len(times) / tot
+    sample = f"{nq_s} of {NQ} queries x {nt} DB rows per step (whole DB, query subset; extrapolates linearly)"
+    line = {"impl": "reference", "metric": "hamming_512b_comparisons_per_s", "value": v, "unit": "comparisons/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": v / PUBLISHED_CMP_S, "dtype": "u64 popcount",
+            "data": "synthetic",
+            "config": {"workload": "C4 map relocalization: 50k queries x 2M-row DB, 512-bit descriptors, 2-NN",
+                       "nQ": NQ, "nT": nt, "cpu_path": "openMVG ArrayMatcherBruteForce<uchar,Hamming> + NNdistanceRatio(0.8), std::async over all cores"
+                       if kind == "reference" else "oracle port of CUDAK2NN.cu (OpenMP)"},
+            "cpu_baseline": {"value": v, "unit": "comparisons/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": v, "unit": "comparisons/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def c2_extra(clb, torch, synth):
+    """config 2 (1280x720 pair, 8 levels): detect+describe per frame and the pair match, device-timed."""
+    w, h = 1280, 720
+    a, b, _ = synth.frame_pair(w, h, 0)
+    det = clb.Detector(w, h, maxkp=120000)
+    clb.set_timing(True)
+    res = {}
+    pin = torch.empty((h, w), dtype=torch.uint8).pin_memory(); pin.numpy()[:] = a
+    img_host = pin.numpy()
+    for it in range(4):
+        ka, da = det.detect_and_describe(img_host)
+    st = {k: clb.last_kernel_ms(k) for k in ("resize", "fast", "describe")}
+    n = len(ka)
+    ts = []
+    for it in range(10):
+        t0 = time.perf_counter(); det.detect_and_describe(img_host); ts.append(time.perf_counter() - t0)
+    e2e_ms = 1e3 * float(np.median(ts))
+    ws, hs, _ = det.level_dims(w, h)
+    pyr_bytes = sum(x * y for x, y in zip(ws, hs))
+    res["frame"] = f"{w}x{h}, 8 levels x1.2, FAST thresh 40"
+    res["keypoints"] = int(n)
+    res["stage_ms"] = st
+    res["detect_describe_e2e_ms"] = e2e_ms
+    res["frames_per_s_e2e"] = 1e3 / e2e_ms
+    res["frames_per_s_kernels"] = 1e3 / max(1e-9, sum(st.values()))
+    res["algorithmic_GBps"] = {"resize": pyr_bytes / st["resize"] / 1e6 if st["resize"] else None,
+                               "fast": (pyr_bytes + 20 * n) / st["fast"] / 1e6 if st["fast"] else None,
+                               "describe": 4180 * n / st["describe"] / 1e6 if st["describe"] else None}
+    ka, da = ka.copy(), da.copy()
+    kb, db = det.detect_and_describe(b)
+    m = clb.Matcher(maxkp=len(da) + len(db) + 16)
+    for it in range(3):
+        m.compute_matches(da, db, 40)
+    res["pair_match_ms"] = clb.last_kernel_ms("match") + clb.last_kernel_ms("merge")
+    res["pair_match_cmp_per_s"] = len(da) * len(db) / (res["pair_match_ms"] * 1e-3)
+    clb.set_timing(False)
+    det.close(); m.close()
+    return res
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    import coloc_b200 as clb
+    from coloc_b200 import shard, synth
+    clb.lib()
+    dev = torch.device("cuda", local_rank)
+    lo, hi = shard.shard_range(NT, rank, world)
+    T_host = torch.from_numpy(make_db_shard(lo, hi).view(np.int64)).pin_memory()
+    Qn, src = make_queries(NQ, NT)
+    Q_host = torch.from_numpy(Qn.view(np.int64)).pin_memory()
+    dT = T_host.to(dev); dQ = Q_host.to(dev)
+    matcher = clb.Matcher(maxkp=max(hi - lo, NQ) + 16, device=local_rank)
+    sm = shard.ShardedMatcher(matcher)
+    sm.set_shard_dev(dT, lo)
+    out = torch.zeros((3, NQ), dtype=torch.int32, device=dev)
+    parts = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
+    gath = torch.empty((world, NQ, 4), dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        sm.match_dev(dQ, NQ, THRESH, out, parts, gath)
+
+    def step_e2e():
+        # the user-facing call with HOST buffers: H2D of this rank's DB rows and the queries, match, D2H of match[]
+        t = T_host.to(dev, non_blocking=True); q = Q_host.to(dev, non_blocking=True)
+        sm.set_shard_dev(t, lo)
+        sm.match_dev(q, NQ, THRESH, out, parts, gath)
+        res = out[0].cpu()
+        sm.set_shard_dev(dT, lo)
+        return res
+
+    # pipe roofline denominator, measured now on this GPU (MEASURED_PEAKS.json has no POPC figure)
+    pipes = clb.microbench_pipes(local_rank)
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local_rank); sampler.start()
+    clb.set_timing(True)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = clb.launch_count()
+    kernel_ms = []
+    barrier()
+    for i in range(args.steps):
+        flush.fill_(i & 0xFF)                          # L2 flush between steps, outside the event pair
+        ev[i][0].record(); step_resident(); ev[i][1].record()
+        torch.cuda.synchronize()
+        kernel_ms.append(clb.last_kernel_ms("match"))
+    barrier()
+    launches = clb.launch_count() - launches0
+    clb.set_timing(False)
+    my_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop()
+
+    # correctness guard inside the bench (not timed): planted matches recovered
+    match = out[0].cpu().numpy()
+    t = src >= 0
+    recovered = float((match[t] == src[t]).mean())
+
+    # e2e
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    e_ev0 = torch.cuda.Event(enable_timing=True); e_ev1 = torch.cuda.Event(enable_timing=True)
+    e_ev0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    e_ev1.record(); torch.cuda.synchronize()
+    my_e2e_ms = e_ev0.elapsed_time(e_ev1)
+    barrier()
+
+    tm = torch.tensor([my_ms, my_e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    tot_ms, e2e_ms = tm.tolist()
+    if rank != 0:
+        return
+    cmp_per_step = float(NQ) * float(NT)
+    value = cmp_per_step * args.steps / (tot_ms * 1e-3)
+    e2e = cmp_per_step * args.steps / (e2e_ms * 1e-3)
+    # roofline of the dominant kernel (match_kernel): algorithmic 16 POPC32 per comparison
+    k_ms = float(np.mean(kernel_ms))
+    ach = 16.0 * NQ * (hi - lo) / (k_ms * 1e-3) / 1e9          # G POPC32/s this rank's kernel achieved
+    peak = pipes["popc_gops"]
+    line = {"metric": "hamming_512b_comparisons_per_s", "value": value, "unit": "comparisons/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": tot_ms / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": value / PUBLISHED_CMP_S,
+            "dtype": "u32 xor/popc", "data": "synthetic",
+            "config": {"workload": "C4 map relocalization: 50k queries x 2M-row DB, 512-bit descriptors, 2-NN + margin test",
+                       "nQ": NQ, "nT": NT, "threshold": THRESH, "parallelism": f"db-rows x{world}",
+                       "l2": "256 MiB device fill between steps, outside the per-step event pairs",
+                       "planted_match_recall": recovered},
+            "e2e": {"value": e2e, "unit": "comparisons/s",
+                    "h2d_bytes_per_step": int(T_host.numel() * 8 + Q_host.numel() * 8), "d2h_bytes_per_step": int(NQ * 4)},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "popc", "achieved": ach, "peak": peak, "unit": "G POPC32/s", "frac": ach / peak, "traffic": None,
+                         "kernel": "clb::match_kernel<4,2>", "kernel_ms": k_ms,
+                         "note": "INT/POPC-pipe bound (north_star); peak = dependent-free POPC stream measured in this run "
+                                 "(clb_microbench_pipes); the kernel issues 8 POPC + 32 LOP3 per comparison (carry-save tree), "
+                                 "so frac > 1 is legitimate; HBM traffic is ~0.2 % of peak",
+                         "pipes": pipes},
+            }
+    if world == 1:
+        # CPU baseline beside it (bounded sample) + config-2 stage numbers
+        import oracle as O
+        kind = "reference" if O.ref_cpu() is not None else "port"
+        Tn = T_host.numpy().view(np.uint64)
+        nq_s = 256
+        t0 = time.perf_counter()
+        (O.ref_bruteforce_2nn(Tn, Qn[:nq_s], 0.8) if kind == "reference" else O.match_2nn(Qn[:nq_s], Tn, THRESH))
+        dt = time.perf_counter() - t0
+        if dt < 5.0:
+            nq_s = int(min(NQ, nq_s * 10.0 / max(dt, 1e-3)))
+            t0 = time.perf_counter()
+            (O.ref_bruteforce_2nn(Tn, Qn[:nq_s], 0.8) if kind == "reference" else O.match_2nn(Qn[:nq_s], Tn, THRESH))
+            dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": nq_s * float(NT) / dt, "unit": "comparisons/s", "cores": os.cpu_count(), "kind": kind,
+                                "sample": f"{nq_s} of {NQ} queries x {NT} DB rows, one pass ({dt:.1f} s)"}
+        try:
+            line["extra"] = {"c2_pipeline": c2_extra(clb, torch, synth)}
+        except Exception as e:   # the headline number must still print
+            line["extra"] = {"c2_pipeline_error": repr(e)}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -87,9 +87,9 @@ def set_param(name, value):
 
 
 def microbench_pipes(device=0):
-    out = (C.c_double * 6)()
+    out = (C.c_double * 8)()
     _check(lib().clb_microbench_pipes(int(device), out))
-    k = ["popc_per_clk_sm", "lop3_per_clk_sm", "mixed_popc_per_clk_sm", "mixed_lop3_per_clk_sm", "sm_mhz", "sm_count"]
+    k = ["popc_per_clk_sm", "lop3_per_clk_sm", "mixed_popc_per_clk_sm", "mixed_lop3_per_clk_sm", "sm_mhz", "sm_count", "popc_gops", "lop3_gops"]
     return dict(zip(k, [float(v) for v in out]))
 
 

@@ -102,10 +102,10 @@ int clb_set_param(const char* name, int value) {
     else return CLB_EINVAL;
     return CLB_OK;
 }
-int clb_microbench_pipes(int device, double* out6) {
-    if (!out6) return CLB_EINVAL;
+int clb_microbench_pipes(int device, double* out8) {
+    if (!out8) return CLB_EINVAL;
     CLB_CUDA(cudaSetDevice(device));
-    return microbench_pipes(out6);
+    return microbench_pipes(out8);
 }
 
 int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector** out) {

@@ -101,6 +101,6 @@ int launch_describe(const LevelTable& lt, const clb_keypoint* d_kps, int n, cons
 int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t s);
 int latch_init();   // uploads the triplet table
 // microbench.cu
-int microbench_pipes(double* out6);
+int microbench_pipes(double* out8);
 
 }  // namespace clb

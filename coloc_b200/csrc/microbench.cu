@@ -74,6 +74,9 @@ int microbench_pipes(double* out) {
         out[4] = mean / (ms_mode[2] * 1e-3) / 1e6;
     }
     out[5] = sms;
+    // chip-level rates straight from wall time (no clock assumption): ops / event time
+    out[6] = 2.0 * threads * iters * 8.0 * sms / (ms_mode[0] * 1e-3) / 1e9;    // G POPC32/s, POPC-only stream
+    out[7] = 2.0 * threads * iters * 16.0 * sms / (ms_mode[1] * 1e-3) / 1e9;   // G LOP3/s, LOP3-only stream
     delete[] h_cyc; cudaFree(d_out); cudaFree(d_cyc); cudaEventDestroy(e0); cudaEventDestroy(e1);
     (void)khz;
     return CLB_OK;

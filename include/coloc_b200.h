@@ -147,8 +147,9 @@ int  clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int npar
 /* pipe micro-benchmarks that back the match roofline: dependent-free POPC / LOP3
  * streams and a mixed stream; results in ops per clock per SM and the SM clock seen.
  * out[0]=popc/clk/SM out[1]=lop3/clk/SM out[2]=mixed popc/clk/SM out[3]=mixed lop3/clk/SM
- * out[4]=SM MHz during the run  out[5]=SM count */
-int  clb_microbench_pipes(int device, double* out6);
+ * out[4]=SM MHz during the run  out[5]=SM count
+ * out[6]=chip G POPC32/s (wall time)  out[7]=chip G LOP3/s (wall time) */
+int  clb_microbench_pipes(int device, double* out8);
 /* number of kernels this library launched on the calling process so far (bench's gpu_launches) */
 int64_t clb_launch_count(void);
 /* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */

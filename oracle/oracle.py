@@ -236,3 +236,39 @@ def sincos_many(a):
     s = np.zeros(a.shape, np.float32); c = np.zeros(a.shape, np.float32)
     lib().orc_sincos_many(_p(a, _f32p), _p(s, _f32p), _p(c, _f32p), C.c_long(a.size))
     return s, c
+
+
+# ------------------------------------------------------------------ reference (GPU) wrappers
+def ref_gpu_resize_level(img, f, dw, dh):
+    """the reference's CUDALERP kernel (src/CUDALERP.cu) on the GPU."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    out = np.zeros((dh, dw), np.uint8)
+    rc = ref_gpu().ref_gpu_lerp(_p(img, _u8p), w, h, C.c_float(float(f)), _p(out, _u8p), dw, dh)
+    assert rc == 0
+    return out
+
+
+def ref_gpu_latch(levels, kps, iters=1):
+    """the reference's CLATCH kernel (src/CLATCH.cu) on the GPU.  Returns (desc, kernel_ms)."""
+    levels = [np.ascontiguousarray(l, np.uint8) for l in levels]
+    L = len(levels)
+    ptrs = (C.c_void_p * L)(*[l.ctypes.data for l in levels])
+    ws = np.array([l.shape[1] for l in levels], np.int32); hs = np.array([l.shape[0] for l in levels], np.int32)
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    desc = np.zeros((len(kps), 8), np.uint64)
+    ms = C.c_float(0)
+    rc = ref_gpu().ref_gpu_latch(ptrs, _p(ws, _i32p), _p(hs, _i32p), L, kps.ctypes.data_as(C.c_void_p), len(kps),
+                                 _p(desc, _u64p), int(iters), C.byref(ms))
+    assert rc == 0
+    return desc, ms.value
+
+
+def ref_gpu_k2nn(Q, T, threshold, iters=1):
+    """the reference's CUDAK2NN kernel (src/CUDAK2NN.cu) on the GPU.  Returns (match, kernel_ms)."""
+    Q = np.ascontiguousarray(Q, np.uint64).reshape(-1, 8); T = np.ascontiguousarray(T, np.uint64).reshape(-1, 8)
+    m = np.zeros(len(Q), np.int32)
+    ms = C.c_float(0)
+    rc = ref_gpu().ref_gpu_k2nn(_p(Q, _u64p), len(Q), _p(T, _u64p), len(T), int(threshold), _p(m, _i32p), int(iters), C.byref(ms))
+    assert rc == 0
+    return m, ms.value
