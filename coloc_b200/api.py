@@ -93,6 +93,14 @@ def microbench_pipes(device=0):
     return dict(zip(k, [float(v) for v in out]))
 
 
+def _sarg(stream):
+    """cudaStream_t argument: None -> NULL (= the object's own stream); a torch stream handle of 0 (the legacy
+    default stream) is passed as cudaStreamLegacy (0x1) so that it is not mistaken for NULL."""
+    if stream is None:
+        return C.c_void_p(0)
+    return C.c_void_p(int(stream) if int(stream) != 0 else 1)
+
+
 def _dptr(t):
     """device pointer of a torch CUDA tensor (plumbing only); ints pass through."""
     if t is None:
@@ -147,7 +155,7 @@ class Detector:
         h, w = d_img.shape
         pk = C.c_void_p(); pd = C.c_void_p(); n = C.c_int(0)
         _check(lib().clb_detect_describe_dev(self._h, _dptr(d_img), w, h, d_img.stride(0), C.byref(pk), C.byref(pd), C.byref(n),
-                                             C.c_void_p(stream or 0)))
+                                             _sarg(stream)))
         return pk.value, pd.value, n.value
 
     def pyramid(self, img):
@@ -248,12 +256,12 @@ class Matcher:
     # ---- device-pointer entry points (torch CUDA tensors as plain buffers) -----------------
     def match_dev(self, dQ, nQ, dT, nT, threshold, d_match, d_best=None, d_second=None, stream=None):
         _check(lib().clb_match_2nn_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), int(threshold),
-                                       _dptr(d_match), _dptr(d_best), _dptr(d_second), C.c_void_p(stream or 0)))
+                                       _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))
 
     def match_partial_dev(self, dQ, nQ, dT, nT, t_base, d_partial, stream=None):
         _check(lib().clb_match_partial_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), C.c_int64(int(t_base)),
-                                           _dptr(d_partial), C.c_void_p(stream or 0)))
+                                           _dptr(d_partial), _sarg(stream)))
 
     def merge_partials_dev(self, d_parts, nparts, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
         _check(lib().clb_merge_partials_dev(self._h, _dptr(d_parts), int(nparts), int(nQ), int(threshold),
-                                            _dptr(d_match), _dptr(d_best), _dptr(d_second), C.c_void_p(stream or 0)))
+                                            _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))

@@ -73,7 +73,7 @@ class ShardedMatcher:
         """device-resident step.  d_out: int32 CUDA tensor [3, nQ] (match, best, second).  Enqueues on torch's
         current stream; returns nothing."""
         torch, dist = self.torch, self.dist
-        stream = torch.cuda.current_stream().cuda_stream
+        stream = torch.cuda.current_stream().cuda_stream   # 0 (legacy default) is mapped to cudaStreamLegacy by the binding
         if self.world == 1:
             self.m.match_dev(dQ, nQ, self.dT, self.n_local, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
             return

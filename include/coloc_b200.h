@@ -9,7 +9,8 @@
  * Host-pointer entry points (suffix-less) have the reference's blocking semantics: they copy
  * inputs H2D, run, copy results D2H and return after a stream sync (GPUDetector.hpp:290,
  * CUDAK2NN.cu:80).  `_dev` entry points take DEVICE pointers plus a cudaStream_t (passed as
- * void*) and only enqueue work.
+ * void*) and only enqueue work; a NULL stream means the object's own (non-blocking) stream, pass
+ * cudaStreamLegacy / cudaStreamPerThread explicitly to use a default stream.
  */
 #ifndef COLOC_B200_H
 #define COLOC_B200_H
