@@ -12,8 +12,38 @@ struct clb_matcher {
     int device, sm_count;
     cudaStream_t stream;
     DevBuf q, t, map, scratch, out;   // out: match | best | second (3 x nQ int32)
+    DevBuf qx, tx, mapx;              // +-1 E4M3 expansions for the tensor-core path (match_tc.cu)
     int n_map;
+    bool mapx_valid;
 };
+
+// Expand the operands when the tensor-core path applies; *Qx / *Tx stay NULL for the POPC path.
+// `map` = T is the resident map (expanded once per clb_set_map, not per query set).
+static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, bool map, cudaStream_t s,
+                      const void** Qx, const void** Tx) {
+    *Qx = nullptr; *Tx = nullptr;
+    if (!tc_wanted(nQ, nT)) return CLB_OK;
+    const size_t qb = tc_q_bytes(nQ), tb = tc_t_bytes(nT);
+    CLB_CUDA(m->qx.reserve(qb));
+    int rc = launch_expand(dQ, nQ, qb, m->qx.p, s);
+    if (rc) return rc;
+    if (map) {
+        if (!m->mapx_valid) {
+            CLB_CUDA(m->mapx.reserve(tb));
+            rc = launch_expand(dT, nT, tb, m->mapx.p, s);
+            if (rc) return rc;
+            m->mapx_valid = true;
+        }
+        *Tx = m->mapx.p;
+    } else {
+        CLB_CUDA(m->tx.reserve(tb));
+        rc = launch_expand(dT, nT, tb, m->tx.p, s);
+        if (rc) return rc;
+        *Tx = m->tx.p;
+    }
+    *Qx = m->qx.p;
+    return CLB_OK;
+}
 
 static int ensure(clb_matcher* m, int nQ, int nT) {
     CLB_CUDA(m->scratch.reserve(match_scratch_bytes(nQ, nT)));
@@ -23,13 +53,16 @@ static int ensure(clb_matcher* m, int nQ, int nT) {
 
 // shared tail of the host entry points: run on device buffers, copy results out
 static int run_host(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold, float ratio,
-                    int32_t* match_out, int32_t* best_out, int32_t* second_out) {
+                    int32_t* match_out, int32_t* best_out, int32_t* second_out, bool map = false) {
     cudaStream_t s = m->stream;
     int rc = ensure(m, nQ, nT);
     if (rc) return rc;
+    const void *Qx, *Tx;
+    rc = prepare_tc(m, dQ, nQ, dT, nT, map, s, &Qx, &Tx);
+    if (rc) return rc;
     int32_t* o = m->out.as<int32_t>();
     rc = launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, ratio,
-                      o, best_out ? o + nQ : nullptr, second_out ? o + 2 * (size_t)nQ : nullptr, nullptr, s);
+                      o, best_out ? o + nQ : nullptr, second_out ? o + 2 * (size_t)nQ : nullptr, nullptr, s, Qx, Tx);
     if (rc) return rc;
     if (match_out) CLB_CUDA(cudaMemcpyAsync(match_out, o, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
     if (best_out) CLB_CUDA(cudaMemcpyAsync(best_out, o + nQ, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
@@ -45,7 +78,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     CLB_CUDA(cudaSetDevice(device));
     clb_matcher* m = new (std::nothrow) clb_matcher();
     if (!m) return CLB_ENOMEM;
-    m->o = *opts; m->device = device; m->n_map = 0; m->stream = nullptr;
+    m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->stream = nullptr;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);
@@ -59,6 +92,7 @@ void clb_matcher_destroy(clb_matcher* m) {
     if (!m) return;
     cudaSetDevice(m->device);
     m->q.release(); m->t.release(); m->map.release(); m->scratch.release(); m->out.release();
+    m->qx.release(); m->tx.release(); m->mapx.release();
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }
@@ -105,8 +139,12 @@ int clb_match_2nn_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
     CLB_CUDA(cudaSetDevice(m->device));
     rc = ensure(m, nQ, nT);
     if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    const void *Qx, *Tx;
+    rc = prepare_tc(m, dQ, nQ, dT, nT, false, s, &Qx, &Tx);
+    if (rc) return rc;
     return launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, 0.f,
-                        d_match_out, d_best_out, d_second_out, nullptr, stream ? (cudaStream_t)stream : m->stream);
+                        d_match_out, d_best_out, d_second_out, nullptr, s, Qx, Tx);
 }
 
 int clb_set_map(clb_matcher* m, const uint64_t* M, int nM) {
@@ -116,6 +154,7 @@ int clb_set_map(clb_matcher* m, const uint64_t* M, int nM) {
     if (nM > 0) CLB_CUDA(cudaMemcpyAsync(m->map.p, M, (size_t)nM * 64, cudaMemcpyHostToDevice, m->stream));
     CLB_CUDA(cudaStreamSynchronize(m->stream));
     m->n_map = nM;
+    m->mapx_valid = false;      // re-expanded lazily by the next clb_match_map that takes the tensor-core path
     return CLB_OK;
 }
 
@@ -127,7 +166,7 @@ int clb_match_map(clb_matcher* m, const uint64_t* Q, int nQ, int threshold,
     CLB_CUDA(m->q.reserve((size_t)nQ * 64));
     CLB_CUDA(cudaMemcpyAsync(m->q.p, Q, (size_t)nQ * 64, cudaMemcpyHostToDevice, m->stream));
     return run_host(m, m->q.as<uint64_t>(), nQ, m->map.as<uint64_t>(), m->n_map, threshold < 0 ? m->o.thresh : threshold, 0.f,
-                    match_out, best_d_out, second_d_out);
+                    match_out, best_d_out, second_d_out, true);
 }
 
 int clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT,
@@ -139,8 +178,12 @@ int clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint
     CLB_CUDA(cudaSetDevice(m->device));
     rc = ensure(m, nQ, nT);
     if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    const void *Qx, *Tx;
+    rc = prepare_tc(m, dQ, nQ, dT, nT, false, s, &Qx, &Tx);
+    if (rc) return rc;
     return launch_match(dQ, nQ, dT, nT, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
-                        nullptr, nullptr, nullptr, d_partial_out, stream ? (cudaStream_t)stream : m->stream);
+                        nullptr, nullptr, nullptr, d_partial_out, s, Qx, Tx);
 }
 
 int clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,

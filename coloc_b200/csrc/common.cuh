@@ -85,9 +85,18 @@ size_t match_scratch_bytes(int nQ, int nT);
 int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t t_base,
                  void* scratch, size_t scratch_bytes, int sm_count,
                  int threshold, float ratio, int32_t* d_match, int32_t* d_best, int32_t* d_second,
-                 clb_partial* d_partial, cudaStream_t s);
+                 clb_partial* d_partial, cudaStream_t s,
+                 const void* Qx = nullptr, const void* Tx = nullptr);   // expanded operands -> tensor-core path
 int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int threshold,
                           int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s);
+// match_tc.cu -- tcgen05 path: +-1 E4M3 expansion of the packed rows, then a tensor-core distance sweep
+bool   tc_wanted(int nQ, int nT);
+size_t tc_q_bytes(int nQ);
+size_t tc_t_bytes(int nT);
+int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s);
+void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, int* tpc_out);
+int launch_match_tc_kernel(const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
+                           uint2* part, cudaStream_t s);
 // pyramid.cu
 int launch_resize(const LevelTable& lt, cudaStream_t s);   // fills levels 1..n-1 from level 0
 // fast.cu

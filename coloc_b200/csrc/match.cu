@@ -277,6 +277,7 @@ size_t match_scratch_bytes(int nQ, int nT) {
     // worst case over the knobs: chunks are at least 256 rows
     size_t max_chunks = (size_t)(nT + 4 * MT_TILE_ROWS - 1) / (4 * MT_TILE_ROWS) + 1;
     if (max_chunks > 4096) max_chunks = 4096;
+    if (max_chunks < 4) max_chunks = 4;
     return max_chunks * (size_t)(nQ > 0 ? nQ : 1) * sizeof(uint2);
 }
 
@@ -293,9 +294,25 @@ static void launch_rq(int hs, dim3 grid, cudaStream_t s, const uint4* Q, int nQ,
 int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t t_base,
                  void* scratch, size_t scratch_bytes, int sm_count,
                  int threshold, float ratio, int32_t* d_match, int32_t* d_best, int32_t* d_second,
-                 clb_partial* d_partial, cudaStream_t s) {
+                 clb_partial* d_partial, cudaStream_t s, const void* Qx, const void* Tx) {
     if (nQ <= 0) return CLB_OK;
     if (((uintptr_t)dQ & 15) || ((uintptr_t)dT & 15)) { snprintf(g_err, sizeof(g_err), "descriptor pointers must be 16-byte aligned"); return CLB_EINVAL; }
+    if (Qx && Tx && nT > 0) {
+        // tensor-core sweep (match_tc.cu) feeding the same per-chunk key pairs into the same merge
+        int qblocks, nchunks, tpc;
+        tc_plan(nQ, nT, sm_count, &qblocks, &nchunks, &tpc);
+        if ((size_t)nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
+        if (nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }
+        uint2* part = reinterpret_cast<uint2*>(scratch);
+        int rc = launch_match_tc_kernel(Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
+        if (rc) return rc;
+        timer("merge").begin(s);
+        merge_chunks_kernel<<<(nQ + 255) / 256, 256, 0, s>>>(part, nchunks, tpc * 128, nQ, nT, (long long)t_base, threshold, ratio,
+                                                            d_match, d_best, d_second, d_partial);
+        timer("merge").end(s);
+        CLB_LAUNCHED();
+        return CLB_OK;
+    }
     MatchPlan p = plan_match(nQ, nT, sm_count);
     if ((size_t)p.nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
     if (p.nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }

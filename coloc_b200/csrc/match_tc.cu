@@ -1,0 +1,378 @@
+// match_tc.cu -- brute-force 512-bit Hamming 2-NN on the 5th-gen tensor cores (tcgen05 + TMEM).
+//
+// Same contract as match.cu (reference src/CUDAK2NN.cu:42-81: ascending scan, first row attaining
+// the minimum wins, `second` = second smallest distance, == best on ties); this file only changes
+// HOW the nQ x nT distance matrix is produced.  sm_100a has no 1-bit MMA, but
+//     hamming(q, t) = (512 - <q', t'>) / 2     with q', t' in {-1, +1}^512
+// and <q', t'> is a K = 512 dot product that tcgen05.mma kind::f8f6f4 computes exactly with E4M3
+// operands (+-1.0) and fp32 accumulation (every partial sum is an integer of magnitude <= 512).
+// One SM then produces 16 distances per clock (8192 MAC/clk) against ~1.4 on the POPC/LOP3 pipes.
+//
+// Pipeline (one CTA per SM, 10 warps, no clusters):
+//   expand_kernel   packed 64-B rows -> +-1 E4M3 bytes, written ONCE in the exact shared-memory image
+//                   the MMA wants: tiles of 128 rows, 4 K-blocks of [128 rows x 128 B], 128-B swizzle
+//                   (16-B chunk c of row r stored at chunk c ^ (r & 7)).  A tile K-block is 16 KB
+//                   contiguous, so plain 1-D bulk copies (cp.async.bulk, SASS UBLKCP) stage it -- no
+//                   tensor maps.
+//   match_tc_kernel warp 0 lane 0: producer -- 2 query tiles (128 KB, resident for the whole sweep),
+//                   then a 6-stage ring of DB K-blocks.  warp 1 lane 0: 32 tcgen05.mma (M=128, N=128,
+//                   K=32) per DB tile into one of two 256-column TMEM buffers; tcgen05.commit frees
+//                   ring slots / publishes the buffer.  warps 2-9: epilogue, one query per thread:
+//                   tcgen05.ld 32 columns at a time; a group of 8 distances is skipped with 4 FMNMX +
+//                   1 compare unless one of them beats the thread's current second best (after the
+//                   first few tiles that is ~1 % of the groups), otherwise the packed (distance, row)
+//                   keys go through the same 3-op best/second update as match.cu.
+//   The per-(chunk, query) key pairs land in the same `partial` array match.cu's merge kernel folds.
+#include "common.cuh"
+
+namespace clb {
+
+int g_match_tc = -1;        // -1 auto, 0 never, 1 always (clb_set_param "match_tc")
+int g_match_tc_chunks = 0;  // 0 = heuristic
+
+static constexpr int TC_TILE = 128;                      // rows per operand tile (UMMA M and N)
+static constexpr int TC_KB = 4;                          // K-blocks of 128 B per row (512 E4M3)
+static constexpr int TC_KB_BYTES = TC_TILE * 128;        // 16 KB
+static constexpr int TC_TILE_BYTES = TC_KB * TC_KB_BYTES;   // 64 KB
+static constexpr int TC_QTILES = 2;                      // query tiles per CTA
+static constexpr int TC_QROWS = TC_QTILES * TC_TILE;     // 256 queries per CTA
+static constexpr int TC_STAGES = 6;
+static constexpr int TC_EPI_WARPS = 8;
+static constexpr int TC_THREADS = 32 * (2 + TC_EPI_WARPS);
+static constexpr int TC_KEY_SHIFT = 22;                  // same key as match.cu: dist << 22 | row-in-chunk
+static constexpr int TC_MAX_TILES_PER_CHUNK = (1 << TC_KEY_SHIFT) / TC_TILE;
+static constexpr int TC_SMEM_A = TC_QTILES * TC_TILE_BYTES;          // 131072
+static constexpr int TC_SMEM_B = TC_STAGES * TC_KB_BYTES;            //  98304
+static constexpr int TC_SMEM_BAR = 256;
+static constexpr int TC_SMEM_TOTAL = TC_SMEM_A + TC_SMEM_B + TC_SMEM_BAR + 1024;   // + alignment slack
+// kind::f8f6f4 instruction descriptor: D=F32 (bits 4-5 = 1), A=B=E4M3 (0), K-major both, N>>3 at 17, M>>4 at 24
+static constexpr uint32_t TC_IDESC = (1u << 4) | ((uint32_t)(TC_TILE >> 3) << 17) | ((uint32_t)(TC_TILE >> 4) << 24);
+
+// ---- PTX helpers ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tc_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// bounded wait: a protocol bug traps (launch error) instead of hanging the GPU
+__device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok, spins = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+        if ((++spins & 1023u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 8000000000ll) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tc_bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// K-major, 128-B swizzle shared-memory matrix descriptor: rows of 128 B, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 32 consecutive 32-bit columns: thread t gets lane (base lane + t)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(taddr) : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- operand expansion ------------------------------------------------------------------------
+// 4 descriptor bits -> 4 E4M3 bytes: bit 1 -> 0x38 (+1.0), bit 0 -> 0xB8 (-1.0)
+__device__ __forceinline__ uint32_t tc_nib(uint32_t x) {
+    return 0xB8B8B8B8u ^ (((x * 0x00204081u) & 0x01010101u) << 7);
+}
+// One thread per 16-byte output chunk, in output order (coalesced stores).  n_pad rows (a multiple
+// of 128 x `tile_multiple`); rows >= n are zero (E4M3 0.0) and masked out again by the consumer.
+__global__ void __launch_bounds__(256)
+expand_kernel(const uint32_t* __restrict__ rows, int n, size_t n_chunks16, uint4* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_chunks16) return;
+    const int cpos = (int)(i & 7), r = (int)((i >> 3) & 127), kb = (int)((i >> 10) & 3);
+    const size_t tile = i >> 12;
+    const int c = cpos ^ (r & 7);
+    const size_t row = tile * TC_TILE + r;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < (size_t)n) {
+        const uint32_t w = __ldg(rows + row * 16 + kb * 4 + (c >> 1));
+        const uint32_t h = (w >> ((c & 1) * 16)) & 0xFFFFu;
+        v.x = tc_nib(h & 15u); v.y = tc_nib((h >> 4) & 15u); v.z = tc_nib((h >> 8) & 15u); v.w = tc_nib(h >> 12);
+    }
+    out[i] = v;
+}
+
+// ---- main kernel ------------------------------------------------------------------------------
+// per-thread epilogue state
+struct TcState { uint32_t best, second; float thr; };
+
+// 32 accumulator columns (DB rows row0 .. row0+31 of the chunk) for this thread's query
+__device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0, TcState& st) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const float m = fmaxf(fmaxf(fmaxf(v[8 * g + 0], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3])),
+                              fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+        if (m > st.thr) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float x = v[8 * g + e];
+                if (x > st.thr) {   // thr only rises, so testing against the group-entry value is exact
+                    const uint32_t d = (uint32_t)(512 - __float2int_rn(x)) >> 1;
+                    const uint32_t key = (d << TC_KEY_SHIFT) | (row0 + 8 * g + e);
+                    const uint32_t mx = max(key, st.best);
+                    st.second = min(st.second, mx);
+                    st.best = min(st.best, key);
+                }
+            }
+            st.thr = st.second == 0xFFFFFFFFu ? -1e30f : (float)(512 - 2 * (int)(st.second >> TC_KEY_SHIFT));
+        }
+    }
+}
+
+// One 128-column accumulator tile: four 32-column TMEM loads, the next one in flight while the
+// current one is scanned; the buffer is handed back to the MMA warp as soon as the last load landed.
+template <bool MASKED>
+__device__ __forceinline__ void tc_epilogue_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcState& st) {
+    float va[32], vb[32];
+    tc_ld32(t, va);
+    tc_wait_ld();
+    tc_ld32(t + 32, vb);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (i >= valid) va[i] = -1e30f;
+    }
+    tc_process32(va, row0, st);
+    tc_wait_ld();
+    tc_ld32(t + 64, va);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (32 + i >= valid) vb[i] = -1e30f;
+    }
+    tc_process32(vb, row0 + 32, st);
+    tc_wait_ld();
+    tc_ld32(t + 96, vb);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (64 + i >= valid) va[i] = -1e30f;
+    }
+    tc_process32(va, row0 + 64, st);
+    tc_wait_ld();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) tc_mbar_arrive(bar_release);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) if (96 + i >= valid) vb[i] = -1e30f;
+    }
+    tc_process32(vb, row0 + 96, st);
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+match_tc_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                uint2* __restrict__ partial) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;               // 128-B swizzle atoms need 1024-B alignment
+    const uint32_t sA = base, sB = base + TC_SMEM_A, sBar = sB + TC_SMEM_B;
+    const uint32_t bar_full = sBar, bar_empty = sBar + 8 * TC_STAGES, bar_a = sBar + 16 * TC_STAGES;
+    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 16, tmem_slot = bar_tempty + 16;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
+        tc_mbar_init(bar_a, 1);
+        for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {   // TMEM: all 512 columns (two 256-column accumulator buffers), one CTA per SM
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== producer =====
+            const uint8_t* qsrc = Qx + (size_t)blockIdx.x * TC_SMEM_A;
+            tc_mbar_expect_tx(bar_a, TC_SMEM_A);
+            for (int i = 0; i < TC_QTILES * TC_KB; ++i)
+                tc_bulk_load(sA + i * TC_KB_BYTES, qsrc + (size_t)i * TC_KB_BYTES, TC_KB_BYTES, bar_a);
+            const uint8_t* tsrc = Tx + (size_t)tile0 * TC_TILE_BYTES;
+            const int nit = ntiles * TC_KB;
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % TC_STAGES;
+                tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC_STAGES) & 1) ^ 1));
+                tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
+                tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            tc_mbar_wait(bar_a, 0);
+            tc_fence_after();
+            int it = 0;
+            for (int j = 0; j < ntiles; ++j) {
+                const int buf = j & 1;
+                tc_mbar_wait(bar_tempty + 8 * buf, (uint32_t)(((j >> 1) & 1) ^ 1));
+                tc_fence_after();
+                for (int kb = 0; kb < TC_KB; ++kb, ++it) {
+                    const int s = it % TC_STAGES;
+                    tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC_STAGES) & 1));
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint64_t bdesc = tc_desc(sB + s * TC_KB_BYTES + k * 32);
+#pragma unroll
+                        for (int m = 0; m < TC_QTILES; ++m) {
+                            const uint64_t adesc = tc_desc(sA + m * TC_TILE_BYTES + kb * TC_KB_BYTES + k * 32);
+                            tc_mma(tmem + (uint32_t)(buf * 256 + m * TC_TILE), adesc, bdesc, (uint32_t)((kb | k) != 0));
+                        }
+                    }
+                    tc_commit(bar_empty + 8 * s);          // ring slot free once these MMAs have read it
+                }
+                tc_commit(bar_tfull + 8 * buf);            // accumulators of tile j complete
+            }
+        }
+    } else {
+        // ===== epilogue: one query per thread =====
+        const int quarter = warp & 3;                      // TMEM lane quarter this warp may read
+        const int m = (warp - 2) >> 2;                     // which query tile (column half of the buffer)
+        const int qi = blockIdx.x * TC_QROWS + m * TC_TILE + quarter * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(m * TC_TILE);
+        TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
+        const int full_tiles = chunk_rows / TC_TILE;         // a ragged DB leaves one masked tile at the end
+        for (int j = 0; j < ntiles; ++j) {
+            const int buf = j & 1;
+            tc_mbar_wait(bar_tfull + 8 * buf, (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            const uint32_t t = tbase + (uint32_t)(buf * 256);
+            if (j < full_tiles) tc_epilogue_tile<false>(t, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * buf, lane, st);
+            else                tc_epilogue_tile<true>(t, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * buf, lane, st);
+        }
+        if (qi < nQ) partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(st.best, st.second);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------
+bool tc_wanted(int nQ, int nT) {
+    if (g_match_tc == 0 || nQ <= 0 || nT <= 0) return false;
+    if (g_match_tc > 0) return true;
+    return (long long)nQ * (long long)nT >= (1ll << 24);    // below that the expansion passes dominate
+}
+
+size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * TC_SMEM_A; }
+size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * TC_TILE_BYTES; }
+
+int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s) {
+    if (out_bytes == 0) return CLB_OK;
+    const size_t chunks = out_bytes / 16;
+    const size_t blocks = (chunks + 255) / 256;
+    if (blocks > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "descriptor set too large to expand"); return CLB_EINVAL; }
+    timer("expand").begin(s);
+    expand_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
+    timer("expand").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+// choose the DB chunk count: fewest chunks whose CTA count fills whole waves of `sm_count` SMs
+void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, int* tpc_out) {
+    const int qblocks = (nQ + TC_QROWS - 1) / TC_QROWS;
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int min_chunks = (total_tiles + TC_MAX_TILES_PER_CHUNK - 1) / TC_MAX_TILES_PER_CHUNK;
+    int max_chunks = total_tiles / 4;                       // >= 4 tiles (512 rows) per chunk
+    if (max_chunks > 256) max_chunks = 256;
+    if (max_chunks < min_chunks) max_chunks = min_chunks;
+    if (max_chunks < 1) max_chunks = 1;
+    int best_c = min_chunks > 0 ? min_chunks : 1;
+    if (g_match_tc_chunks > 0) {
+        best_c = g_match_tc_chunks < max_chunks ? g_match_tc_chunks : max_chunks;
+        if (best_c < min_chunks) best_c = min_chunks;
+    } else {
+        double best_eff = -1.0;
+        for (int c = best_c; c <= max_chunks; ++c) {
+            const int tpc = (total_tiles + c - 1) / c;
+            const int real_c = (total_tiles + tpc - 1) / tpc;
+            const long long ctas = (long long)qblocks * real_c;
+            const long long waves = (ctas + sm_count - 1) / sm_count;
+            // work done / work slots: the busiest SM runs `waves` CTAs of tpc tiles
+            const double eff = (double)qblocks * total_tiles / ((double)waves * sm_count * tpc);
+            if (eff > best_eff + 0.02) { best_eff = eff; best_c = c; }
+            if (best_eff >= 0.95) break;
+        }
+    }
+    const int tpc = (total_tiles + best_c - 1) / best_c;
+    *qblocks_out = qblocks;
+    *tpc_out = tpc > 0 ? tpc : 1;
+    *nchunks_out = total_tiles > 0 ? (total_tiles + *tpc_out - 1) / *tpc_out : 0;
+}
+
+int launch_match_tc_kernel(const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
+                           uint2* part, cudaStream_t s) {
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    CLB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+        CLB_CUDA(cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
+        if (dev >= 0 && dev < 64) attr_done[dev] = true;
+    }
+    dim3 grid(qblocks, nchunks);
+    timer("match").begin(s);
+    match_tc_kernel<<<grid, TC_THREADS, TC_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
+                                                          reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part);
+    timer("match").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+}  // namespace clb
