@@ -12,7 +12,7 @@ namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg;
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -99,6 +99,8 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_hs")) { if (value < 0 || value > 3) return CLB_EINVAL; g_match_hs = value; }
     else if (!strcmp(name, "match_chunks")) { if (value < 0) return CLB_EINVAL; g_match_chunks = value; }
     else if (!strcmp(name, "match_tc")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_tc = value; }
+    else if (!strcmp(name, "match_tc_ver")) { if (value != 1 && value != 2) return CLB_EINVAL; g_match_tc_ver = value; }
+    else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
     else return CLB_EINVAL;

@@ -24,9 +24,13 @@ static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
     *Qx = nullptr; *Tx = nullptr;
     if (!tc_wanted(nQ, nT)) return CLB_OK;
     const size_t qb = tc_q_bytes(nQ), tb = tc_t_bytes(nT);
-    CLB_CUDA(m->qx.reserve(qb));
-    int rc = launch_expand(dQ, nQ, qb, m->qx.p, s);
-    if (rc) return rc;
+    int rc = CLB_OK;
+    if (tc_needs_qx()) {
+        CLB_CUDA(m->qx.reserve(qb));
+        rc = launch_expand(dQ, nQ, qb, m->qx.p, s);
+        if (rc) return rc;
+        *Qx = m->qx.p;
+    }
     if (map) {
         if (!m->mapx_valid) {
             CLB_CUDA(m->mapx.reserve(tb));
@@ -41,7 +45,6 @@ static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
         if (rc) return rc;
         *Tx = m->tx.p;
     }
-    *Qx = m->qx.p;
     return CLB_OK;
 }
 

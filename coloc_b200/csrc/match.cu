@@ -297,14 +297,14 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
                  clb_partial* d_partial, cudaStream_t s, const void* Qx, const void* Tx) {
     if (nQ <= 0) return CLB_OK;
     if (((uintptr_t)dQ & 15) || ((uintptr_t)dT & 15)) { snprintf(g_err, sizeof(g_err), "descriptor pointers must be 16-byte aligned"); return CLB_EINVAL; }
-    if (Qx && Tx && nT > 0) {
+    if (Tx && nT > 0) {
         // tensor-core sweep (match_tc.cu) feeding the same per-chunk key pairs into the same merge
         int qblocks, nchunks, tpc;
         tc_plan(nQ, nT, sm_count, &qblocks, &nchunks, &tpc);
         if ((size_t)nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
         if (nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }
         uint2* part = reinterpret_cast<uint2*>(scratch);
-        int rc = launch_match_tc_kernel(Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
+        int rc = launch_match_tc_kernel(dQ, Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
         if (rc) return rc;
         timer("merge").begin(s);
         merge_chunks_kernel<<<(nQ + 255) / 256, 256, 0, s>>>(part, nchunks, tpc * 128, nQ, nT, (long long)t_base, threshold, ratio,

@@ -29,6 +29,8 @@ namespace clb {
 
 int g_match_tc = -1;        // -1 auto, 0 never, 1 always (clb_set_param "match_tc")
 int g_match_tc_chunks = 0;  // 0 = heuristic
+int g_match_tc_dbg = 0;     // timing experiments (v1 kernel): 1 no TMEM reads, 2 TMEM reads only, 3 no MMAs
+int g_match_tc_ver = 2;     // 1 = queries in shared memory (SS), 2 = queries in TMEM (TS)
 
 static constexpr int TC_TILE = 128;                      // rows per operand tile (UMMA M and N)
 static constexpr int TC_KB = 4;                          // K-blocks of 128 B per row (512 E4M3)
@@ -80,16 +82,23 @@ __device__ __forceinline__ void tc_bulk_load(uint32_t dst, const void* src, uint
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// one lane of a converged warp (the same one every time for a full mask); lets ptxas keep the
+// uniform-datapath instructions (UTCQMMA, UBLKCP, UTCBAR) out of per-lane ELECT/BRA loops
+__device__ __forceinline__ bool tc_elect_one() {
+    uint32_t pred = 0;
+    asm volatile("{\n\t.reg .pred px;\n\telect.sync _|px, 0xFFFFFFFF;\n\t@px mov.s32 %0, 1;\n\t}" : "+r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // K-major, 128-B swizzle shared-memory matrix descriptor: rows of 128 B, 8-row groups 1024 B apart
 __device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
-__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate, uint32_t idesc = TC_IDESC) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate) : "memory");
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -201,7 +210,7 @@ __device__ __forceinline__ void tc_epilogue_tile(uint32_t t, uint32_t row0, int 
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 match_tc_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
-                uint2* __restrict__ partial) {
+                uint2* __restrict__ partial, int dbg) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t raw = tc_smem_u32(tc_smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;               // 128-B swizzle atoms need 1024-B alignment
@@ -233,47 +242,56 @@ match_tc_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restric
     const uint32_t tmem = *tmem_slot_ptr;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== producer =====
-            const uint8_t* qsrc = Qx + (size_t)blockIdx.x * TC_SMEM_A;
+        // ===== producer (whole warp converged, one elected lane issues) =====
+        const uint8_t* qsrc = Qx + (size_t)blockIdx.x * TC_SMEM_A;
+        if (tc_elect_one()) {
             tc_mbar_expect_tx(bar_a, TC_SMEM_A);
             for (int i = 0; i < TC_QTILES * TC_KB; ++i)
                 tc_bulk_load(sA + i * TC_KB_BYTES, qsrc + (size_t)i * TC_KB_BYTES, TC_KB_BYTES, bar_a);
-            const uint8_t* tsrc = Tx + (size_t)tile0 * TC_TILE_BYTES;
-            const int nit = ntiles * TC_KB;
-            for (int it = 0; it < nit; ++it) {
-                const int s = it % TC_STAGES;
-                tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC_STAGES) & 1) ^ 1));
+        }
+        __syncwarp();
+        const uint8_t* tsrc = Tx + (size_t)tile0 * TC_TILE_BYTES;
+        const int nit = ntiles * TC_KB;
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC_STAGES;
+            tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC_STAGES) & 1) ^ 1));
+            if (tc_elect_one()) {
                 tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
                 tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
             }
+            __syncwarp();
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
-            tc_mbar_wait(bar_a, 0);
+        // ===== MMA issuer (whole warp converged, one elected lane issues) =====
+        tc_mbar_wait(bar_a, 0);
+        tc_fence_after();
+        const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        int it = 0;
+        for (int j = 0; j < ntiles; ++j) {
+            const int buf = j & 1;
+            tc_mbar_wait(bar_tempty + 8 * buf, (uint32_t)(((j >> 1) & 1) ^ 1));
             tc_fence_after();
-            int it = 0;
-            for (int j = 0; j < ntiles; ++j) {
-                const int buf = j & 1;
-                tc_mbar_wait(bar_tempty + 8 * buf, (uint32_t)(((j >> 1) & 1) ^ 1));
+            for (int kb = 0; kb < TC_KB; ++kb, ++it) {
+                const int s = it % TC_STAGES;
+                tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC_STAGES) & 1));
                 tc_fence_after();
-                for (int kb = 0; kb < TC_KB; ++kb, ++it) {
-                    const int s = it % TC_STAGES;
-                    tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC_STAGES) & 1));
-                    tc_fence_after();
+                if (tc_elect_one()) {
+                    const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                    const uint64_t a0 = desc_hi | (uint64_t)(((sA + kb * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                    const uint32_t d0 = tmem + (uint32_t)(buf * 256);
+                    const uint32_t idesc = dbg == 4 ? ((1u << 4) | (8u << 17) | (8u << 24)) : TC_IDESC;
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        const uint64_t bdesc = tc_desc(sB + s * TC_KB_BYTES + k * 32);
 #pragma unroll
                         for (int m = 0; m < TC_QTILES; ++m) {
-                            const uint64_t adesc = tc_desc(sA + m * TC_TILE_BYTES + kb * TC_KB_BYTES + k * 32);
-                            tc_mma(tmem + (uint32_t)(buf * 256 + m * TC_TILE), adesc, bdesc, (uint32_t)((kb | k) != 0));
+                            if (dbg != 3) tc_mma(d0 + (uint32_t)(m * TC_TILE), a0 + (uint64_t)(m * (TC_TILE_BYTES >> 4) + k * 2),
+                                                 b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0), idesc);
                         }
                     }
                     tc_commit(bar_empty + 8 * s);          // ring slot free once these MMAs have read it
+                    if (kb == TC_KB - 1) tc_commit(bar_tfull + 8 * buf);   // accumulators of tile j complete
                 }
-                tc_commit(bar_tfull + 8 * buf);            // accumulators of tile j complete
+                __syncwarp();
             }
         }
     } else {
@@ -289,8 +307,184 @@ match_tc_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restric
             tc_mbar_wait(bar_tfull + 8 * buf, (uint32_t)((j >> 1) & 1));
             tc_fence_after();
             const uint32_t t = tbase + (uint32_t)(buf * 256);
+            if (dbg == 1 || dbg == 2) {      // timing experiments only (results are garbage)
+                if (dbg == 2) {
+                    float va[32];
+                    tc_ld32(t, va); tc_ld32(t + 32, va); tc_ld32(t + 64, va); tc_ld32(t + 96, va);
+                    tc_wait_ld();
+                    if (va[0] == 12345.f) st.best = 0;
+                }
+                tc_fence_before(); __syncwarp();
+                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * buf);
+                continue;
+            }
             if (j < full_tiles) tc_epilogue_tile<false>(t, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * buf, lane, st);
             else                tc_epilogue_tile<true>(t, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * buf, lane, st);
+        }
+        if (qi < nQ) partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(st.best, st.second);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+// ---- v2: query tiles resident in TMEM (A operand from tensor memory) --------------------------------
+// ncu on the kernel above: tensor pipe 62 % active with the shared-memory tensor-read path equally
+// busy -- an SS-mode M=128 x N=128 x K=32 MMA reads 8 KB of shared memory per 64 math cycles, all the
+// bandwidth an SM has, and the bulk copies write into the same banks.  Here the two query tiles are
+// expanded in registers by their epilogue threads and parked in TMEM (columns 0-255: 128 lanes x 128
+// packed words per tile) with tcgen05.st, so each MMA only reads its 4 KB B slice; shared memory is all
+// DB ring (14 K-block stages, 224 KB in flight per SM).  The two 128-column accumulators (columns 256-511)
+// alternate: while the epilogue warps of query tile 0 scan D0, the MMA warp fills D1 from the same DB
+// tile, so there is no second buffer per tile and none is needed.
+static constexpr int TC2_STAGES = 14;
+static constexpr int TC2_SMEM_B = TC2_STAGES * TC_KB_BYTES;          // 229376
+static constexpr int TC2_SMEM_BAR = 512;
+static constexpr int TC2_SMEM_TOTAL = TC2_SMEM_B + TC2_SMEM_BAR + 1024;
+
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                 "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+                 "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+                 ::"r"(taddr),
+                   "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                   "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+                   "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+                   "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+                 : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+match_tc2_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                 uint2* __restrict__ partial, int dbg) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t sB = (raw + 1023u) & ~1023u;
+    const uint32_t sBar = sB + TC2_SMEM_B;
+    const uint32_t bar_full = sBar, bar_empty = sBar + 8 * TC2_STAGES, bar_a = sBar + 16 * TC2_STAGES;
+    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 16, tmem_slot = bar_tempty + 16;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+
+    if (tid == 0) {
+        for (int s = 0; s < TC2_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
+        tc_mbar_init(bar_a, TC_EPI_WARPS);
+        for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC_EPI_WARPS / 2); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===== producer: DB K-blocks, 16 KB each, straight from the pre-swizzled image =====
+        const uint8_t* tsrc = Tx + (size_t)tile0 * TC_TILE_BYTES;
+        const int nit = ntiles * TC_KB;
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC2_STAGES;
+            tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC2_STAGES) & 1) ^ 1));
+            if (tc_elect_one()) {
+                tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
+                tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: D_m (+)= A_m[tmem] x B[smem], m alternating per DB tile =====
+        tc_mbar_wait(bar_a, 0);
+        tc_fence_after();
+        const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        for (int j = 0; j < ntiles; ++j) {
+#pragma unroll
+            for (int m = 0; m < TC_QTILES; ++m) {
+                tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
+                tc_fence_after();
+                for (int kb = 0; kb < TC_KB; ++kb) {
+                    const int it = j * TC_KB + kb;
+                    const int s = it % TC2_STAGES;
+                    if (m == 0) {
+                        tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC2_STAGES) & 1));
+                        tc_fence_after();
+                    }
+                    if (tc_elect_one()) {
+                        const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                        const uint32_t a0 = tmem + (uint32_t)(m * TC_TILE + kb * 32);
+                        const uint32_t d0 = tmem + (uint32_t)(256 + m * TC_TILE);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            tc_mma_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0));
+                        if (m == TC_QTILES - 1) tc_commit(bar_empty + 8 * s);
+                        if (kb == TC_KB - 1) tc_commit(bar_tfull + 8 * m);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===== epilogue warps: first park this thread's query in TMEM, then scan its accumulator row =====
+        const int quarter = warp & 3;
+        const int m = (warp - 2) >> 2;
+        const int qi = blockIdx.x * TC_QROWS + m * TC_TILE + quarter * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+        {
+            uint4 q4[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                q4[i] = qi < nQ ? __ldg(reinterpret_cast<const uint4*>(Q + (size_t)qi * 16) + i) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {                      // 4 packed words -> 32 TMEM columns (128 E4M3)
+                const uint32_t w[4] = {q4[i].x, q4[i].y, q4[i].z, q4[i].w};
+                uint32_t r[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = qi < nQ ? tc_nib((w[c >> 3] >> (4 * (c & 7))) & 15u) : 0u;
+                tc_st32(lane_base + (uint32_t)(m * TC_TILE + 32 * i), r);
+            }
+            tc_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc_mbar_arrive(bar_a);
+        }
+        const uint32_t tbase = lane_base + (uint32_t)(256 + m * TC_TILE);
+        TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
+        const int full_tiles = chunk_rows / TC_TILE;
+        for (int j = 0; j < ntiles; ++j) {
+            tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
+            tc_fence_after();
+            if (dbg == 1 || dbg == 2) {      // timing experiments only (results are garbage)
+                if (dbg == 2) {
+                    float va[32];
+                    tc_ld32(tbase, va); tc_ld32(tbase + 32, va); tc_ld32(tbase + 64, va); tc_ld32(tbase + 96, va);
+                    tc_wait_ld();
+                    if (va[0] == 12345.f) st.best = 0;
+                }
+                tc_fence_before(); __syncwarp();
+                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                continue;
+            }
+            if (j < full_tiles) tc_epilogue_tile<false>(tbase, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * m, lane, st);
+            else                tc_epilogue_tile<true>(tbase, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * m, lane, st);
         }
         if (qi < nQ) partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(st.best, st.second);
     }
@@ -357,19 +551,26 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
     *nchunks_out = total_tiles > 0 ? (total_tiles + *tpc_out - 1) / *tpc_out : 0;
 }
 
-int launch_match_tc_kernel(const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
+bool tc_needs_qx() { return g_match_tc_ver == 1; }
+
+int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s) {
     static bool attr_done[64] = {false};
     int dev = 0;
     CLB_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_done[dev]) {
         CLB_CUDA(cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
+        CLB_CUDA(cudaFuncSetAttribute(match_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_TOTAL));
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     dim3 grid(qblocks, nchunks);
     timer("match").begin(s);
-    match_tc_kernel<<<grid, TC_THREADS, TC_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
-                                                          reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part);
+    if (g_match_tc_ver == 1 && Qx)
+        match_tc_kernel<<<grid, TC_THREADS, TC_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
+                                                              reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
+    else
+        match_tc2_kernel<<<grid, TC_THREADS, TC2_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
+                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
     timer("match").end(s);
     CLB_LAUNCHED();
     return CLB_OK;

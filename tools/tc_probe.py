@@ -31,6 +31,9 @@ def run(m, Q, T, thr, tc):
 
 def main():
     mode = sys.argv[1] if len(sys.argv) > 1 else "quick"
+    global VERS
+    VERS = [int(v) for v in sys.argv[2].split(",")] if len(sys.argv) > 2 else [2]
+    clb.set_param("match_tc_ver", VERS[-1])
     rng = np.random.default_rng(7)
     m = clb.Matcher(maxkp=1000)
     clb.set_timing(True)
@@ -46,15 +49,17 @@ def main():
             Q[0] = T[1]
         for thr in (40,):
             a = run(m, Q, T, thr, 0); t0 = clb.last_kernel_ms("match")
-            b = run(m, Q, T, thr, 1); t1 = clb.last_kernel_ms("match")
-            ok = all(np.array_equal(x, y) for x, y in zip(a, b))
-            bad += not ok
-            print(f"{'PASS' if ok else 'FAIL'} nQ={nQ} nT={nT} thr={thr} popc={t0:.3f} ms tc={t1:.3f} ms "
-                  f"({nQ * nT / max(t1, 1e-6) / 1e6:.1f} G cmp/s) matches={(a[0] >= 0).sum()}", flush=True)
-            if not ok:
-                for name, x, y in zip(("match", "best", "second"), a, b):
-                    d = np.nonzero(x != y)[0]
-                    print(f"   {name}: {len(d)} differ; first {d[:5]} popc={x[d[:5]]} tc={y[d[:5]]}")
+            for ver in VERS:
+                clb.set_param("match_tc_ver", ver)
+                b = run(m, Q, T, thr, 1); t1 = clb.last_kernel_ms("match")
+                ok = all(np.array_equal(x, y) for x, y in zip(a, b))
+                bad += not ok
+                print(f"{'PASS' if ok else 'FAIL'} nQ={nQ} nT={nT} thr={thr} popc={t0:.3f} ms tc v{ver}={t1:.3f} ms "
+                      f"({nQ * nT / max(t1, 1e-6) / 1e6:.1f} G cmp/s) matches={(a[0] >= 0).sum()}", flush=True)
+                if not ok:
+                    for name, x, y in zip(("match", "best", "second"), a, b):
+                        d = np.nonzero(x != y)[0]
+                        print(f"   {name}: {len(d)} differ; first {d[:5]} popc={x[d[:5]]} tc={y[d[:5]]}")
     # adversarial order: distances strictly decreasing along the DB (every row beats the previous best)
     nT = 4096
     q = rand_rows(rng, 1)
