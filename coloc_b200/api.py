@@ -86,6 +86,12 @@ def set_param(name, value):
     _check(lib().clb_set_param(name.encode(), int(value)))
 
 
+def get_param(name):
+    v = C.c_int(0)
+    _check(lib().clb_get_param(name.encode(), C.byref(v)))
+    return int(v.value)
+
+
 def microbench_pipes(device=0):
     out = (C.c_double * 8)()
     _check(lib().clb_microbench_pipes(int(device), out))

@@ -12,7 +12,7 @@ namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path;
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -103,6 +103,18 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
+    else return CLB_EINVAL;
+    return CLB_OK;
+}
+int clb_get_param(const char* name, int* value) {
+    if (!name || !value) return CLB_EINVAL;
+    if (!strcmp(name, "match_rq")) *value = g_match_rq;
+    else if (!strcmp(name, "match_hs")) *value = g_match_hs;
+    else if (!strcmp(name, "match_chunks")) *value = g_match_chunks;
+    else if (!strcmp(name, "match_tc")) *value = g_match_tc;
+    else if (!strcmp(name, "match_tc_ver")) *value = g_match_tc_ver;
+    else if (!strcmp(name, "match_tc_chunks")) *value = g_match_tc_chunks;
+    else if (!strcmp(name, "last_match_path")) *value = g_last_match_path;
     else return CLB_EINVAL;
     return CLB_OK;
 }

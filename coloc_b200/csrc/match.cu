@@ -27,6 +27,8 @@ static constexpr int MT_MAX_CHUNK_ROWS = 1 << MT_KEY_SHIFT;
 int g_match_rq = 0;      // 0 = heuristic
 int g_match_hs = 2;      // carry-save depth: 0 none(16 popc) 1 (11) 2 (8) 3 (5)
 int g_match_chunks = 0;  // 0 = heuristic
+int g_last_match_path = 0;   // 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2 (what the last launch_match used)
+extern int g_match_tc_ver;
 
 // ---- PTX helpers ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -304,6 +306,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
         if ((size_t)nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
         if (nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }
         uint2* part = reinterpret_cast<uint2*>(scratch);
+        g_last_match_path = (g_match_tc_ver == 1 && Qx) ? 1 : 2;
         int rc = launch_match_tc_kernel(dQ, Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
         if (rc) return rc;
         timer("merge").begin(s);
@@ -313,6 +316,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
         CLB_LAUNCHED();
         return CLB_OK;
     }
+    g_last_match_path = 0;
     MatchPlan p = plan_match(nQ, nT, sm_count);
     if ((size_t)p.nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
     if (p.nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }

@@ -155,8 +155,12 @@ int  clb_microbench_pipes(int device, double* out8);
 int64_t clb_launch_count(void);
 /* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */
 int  clb_set_timing(int on);
-/* tuning knobs for experiments: "match_rq" (0,1,2,4), "match_hs" (0..3), "match_chunks" (0 = auto) */
+/* tuning knobs for experiments: "match_rq" (0,1,2,4), "match_hs" (0..3), "match_chunks" (0 = auto) for the
+ * POPC kernel; "match_tc" (-1 auto: tensor-core path from 2^24 comparisons up, 0 never, 1 always),
+ * "match_tc_ver" (1 queries in shared memory, 2 queries in TMEM), "match_tc_chunks" (0 = auto).
+ * clb_get_param also answers "last_match_path": 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2. */
 int  clb_set_param(const char* name, int value);
+int  clb_get_param(const char* name, int* value_out);
 float clb_last_kernel_ms(const char* which);   /* "match", "describe", "fast", "resize", "merge" */
 
 #ifdef __cplusplus

@@ -145,6 +145,75 @@ def test_partial_and_merge(clb, oracle):
     m.close()
 
 
+# ------------------------------------------------------------------ tensor-core path (match_tc.cu)
+@pytest.fixture()
+def tc_forced(clb):
+    """force the tcgen05 kernels at every size (the default picks them from 2^24 comparisons up)"""
+    clb.set_param("match_tc", 1)
+    yield
+    clb.set_param("match_tc", -1); clb.set_param("match_tc_ver", 2); clb.set_param("match_tc_chunks", 0)
+
+
+@pytest.mark.parametrize("ver", [2, 1])
+@pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (3, 1), (7, 5), (33, 64), (64, 65), (128, 128), (255, 257), (256, 129),
+                                   (300, 1000), (1000, 777), (2049, 4100), (5000, 5000)])
+def test_match_tc_vs_oracle(clb, oracle, matcher, tc_forced, nq, nt, ver):
+    clb.set_param("match_tc_ver", ver)
+    T = synth.random_descriptors(nt, 100 + nt)
+    Q, _ = synth.planted_queries(T, nq, 200 + nq)
+    rng = np.random.default_rng(nq * 7 + nt)
+    k = max(1, nq // 4)
+    Q[:k] = T[rng.integers(0, nt, k)]                        # exact hits (distance 0)
+    if nt > 4:
+        T[nt // 2] = T[1]; T[nt - 1] = T[1]                  # duplicated rows -> ties, first index must win
+    for thr in (40, 60, 0):
+        _check_match(clb, oracle, matcher, Q, T, thr)
+    assert clb.get_param("last_match_path") == ver
+
+
+@pytest.mark.parametrize("chunks", [1, 2, 5])
+def test_match_tc_chunking(clb, oracle, matcher, tc_forced, chunks):
+    """DB cut into 1 / 2 / 5 chunks over blockIdx.y: merge keeps first-min-wins across chunk borders"""
+    clb.set_param("match_tc_chunks", chunks)
+    T = synth.random_descriptors(3000, 11); Q, _ = synth.planted_queries(T, 700, 12)
+    T[2900] = T[10]; T[1500] = T[10]; Q[0] = T[10]
+    _check_match(clb, oracle, matcher, Q, T, 40)
+
+
+def test_match_tc_edge_cases(clb, oracle, matcher, tc_forced):
+    test_match_edge_cases(clb, oracle, matcher)
+    # adversarial order: every DB row is closer than the one before it (the epilogue's skip test never fires)
+    nt = 2048
+    q = synth.random_descriptors(1, 77)
+    bits = np.unpackbits(q.view(np.uint8), bitorder="little").reshape(1, 512)
+    Tb = np.repeat(bits, nt, axis=0)
+    for r in range(nt):
+        Tb[r, :511 - (r * 511) // nt] ^= 1
+    T = np.packbits(Tb, axis=1, bitorder="little").view(np.uint64)
+    _check_match(clb, oracle, matcher, np.repeat(q, 130, axis=0), T, 0)
+
+
+def test_match_tc_golden_map_and_shards(clb, oracle, matcher, tc_forced):
+    test_match_golden(clb, matcher)
+    test_match_map_api(clb, oracle, matcher)
+    # a second query set against the same map reuses the cached expansion; a new map invalidates it
+    M2 = synth.random_descriptors(2000, 19); Q2, _ = synth.planted_queries(M2, 300, 20)
+    matcher.set_map_data(M2)
+    for Qs in (Q2, Q2[::-1].copy()):
+        got = matcher.match_with_map(Qs, 60, want_dist=True)
+        ref = oracle.match_2nn(Qs, M2, 60)
+        assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+    test_partial_and_merge(clb, oracle)
+
+
+def test_match_default_path_is_tensor_core_at_size(clb, matcher):
+    T = synth.random_descriptors(5000, 1); Q = synth.random_descriptors(5000, 2)
+    matcher.compute_matches(Q, T, 40)
+    assert clb.get_param("last_match_path") == 2              # 2.5e7 comparisons >= 2^24
+    matcher.compute_matches(Q[:100], T[:100], 40)
+    assert clb.get_param("last_match_path") == 0
+
+
 # ------------------------------------------------------------------ pyramid
 @pytest.mark.parametrize("w,h", [(640, 480), (1280, 720), (333, 251), (64, 48)])
 def test_pyramid_vs_oracle(clb, oracle, w, h):
