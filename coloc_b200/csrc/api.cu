@@ -12,7 +12,7 @@ namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex;
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -43,6 +43,8 @@ struct clb_detector {
     DevBuf stage;        // staging for stage-level entry points
     int* h_total;        // pinned
     size_t level_off[CLB_MAX_LEVELS];
+    LevelTex tex;        // texture views of the pyramid levels for the frame geometry tex_w x tex_h
+    int tex_w, tex_h, tex_n;
 };
 
 static void level_dims(const clb_detector_opts& o, int w, int h, int* ws, int* hs, float* fs) {
@@ -68,10 +70,21 @@ static size_t make_table(clb_detector* d, int w, int h, LevelTable& lt) {
         lt.stride[i] = align_up(lt.w[i] > 0 ? lt.w[i] : 1, 128);
         d->level_off[i] = off;
         off += (size_t)lt.stride[i] * (lt.h[i] > 0 ? lt.h[i] : 1) + 256;
-        off = (off + 255) & ~(size_t)255;
+        off = (off + 511) & ~(size_t)511;          // 512 B: cudaDeviceProp::textureAlignment
     }
     for (int i = 0; i < lt.n; ++i) lt.img[i] = d->pyr.as<uint8_t>() ? d->pyr.as<uint8_t>() + d->level_off[i] : nullptr;
     return off;
+}
+
+// texture views follow the frame geometry (the pyramid buffer itself never moves)
+static int ensure_textures(clb_detector* d, const LevelTable& lt, int w, int h) {
+    if (d->tex_n == lt.n && d->tex_w == w && d->tex_h == h) return CLB_OK;
+    destroy_level_textures(d->tex, d->tex_n);
+    d->tex_n = 0;
+    int rc = make_level_textures(lt, d->tex);
+    if (rc) return rc;
+    d->tex_n = lt.n; d->tex_w = w; d->tex_h = h;
+    return CLB_OK;
 }
 
 extern "C" {
@@ -102,6 +115,7 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_tc_ver")) { if (value != 1 && value != 2) return CLB_EINVAL; g_match_tc_ver = value; }
     else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
+    else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
     else return CLB_EINVAL;
     return CLB_OK;
@@ -134,6 +148,7 @@ int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector*
     clb_detector* d = new (std::nothrow) clb_detector();
     if (!d) return CLB_ENOMEM;
     d->o = *opts; d->device = device; d->h_total = nullptr;
+    memset(&d->tex, 0, sizeof(d->tex)); d->tex_w = d->tex_h = d->tex_n = 0;
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMallocHost(&d->h_total, 64);
@@ -155,6 +170,7 @@ int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector*
 void clb_detector_destroy(clb_detector* d) {
     if (!d) return;
     cudaSetDevice(d->device);
+    destroy_level_textures(d->tex, d->tex_n);
     d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release();
     if (d->h_total) cudaFreeHost(d->h_total);
     if (d->stream) cudaStreamDestroy(d->stream);
@@ -176,12 +192,14 @@ static int check_frame(clb_detector* d, int w, int h, int stride) {
 
 // device pipeline on a level-0 image already inside d->pyr (table lt)
 static int run_pipeline(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
-    int rc = launch_resize(lt, s);
+    int rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
+    if (rc) return rc;
+    rc = launch_resize(lt, s);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
     rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
     if (rc) return rc;
-    return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s);
+    return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex);
 }
 
 int clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h, int stride,
@@ -293,6 +311,7 @@ int clb_describe(clb_detector* d, const uint8_t* const* levels, const int32_t* w
     for (int i = 0; i < nlevels; ++i) {
         lt.w[i] = ws[i]; lt.h[i] = hs[i]; lt.stride[i] = align_up(ws[i] > 0 ? ws[i] : 1, 128); lt.f[i] = 1.f;
         off += (size_t)lt.stride[i] * (hs[i] > 0 ? hs[i] : 1) + 256;
+        off = (off + 511) & ~(size_t)511;
     }
     CLB_CUDA(d->stage.reserve(off));
     off = 0;
@@ -300,13 +319,20 @@ int clb_describe(clb_detector* d, const uint8_t* const* levels, const int32_t* w
         lt.img[i] = d->stage.as<uint8_t>() + off;
         if (levels[i] && ws[i] > 0 && hs[i] > 0)
             CLB_CUDA(cudaMemcpy2DAsync(d->stage.as<uint8_t>() + off, lt.stride[i], levels[i], strides[i], ws[i], hs[i], cudaMemcpyHostToDevice, s));
+        else lt.img[i] = nullptr;
         off += (size_t)lt.stride[i] * (hs[i] > 0 ? hs[i] : 1) + 256;
+        off = (off + 511) & ~(size_t)511;
     }
+    LevelTex tx;
+    int trc = make_level_textures(lt, tx);
+    if (trc) return trc;
     CLB_CUDA(cudaMemcpyAsync(d->kps.p, kps, (size_t)n * sizeof(clb_keypoint), cudaMemcpyHostToDevice, s));
-    int rc = launch_describe(lt, d->kps.as<clb_keypoint>(), n, nullptr, d->o.maxkp, d->desc.as<uint64_t>(), s);
+    int rc = launch_describe(lt, d->kps.as<clb_keypoint>(), n, nullptr, d->o.maxkp, d->desc.as<uint64_t>(), s, &tx);
+    cudaError_t e1 = rc ? cudaSuccess : cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s);
+    cudaError_t e2 = cudaStreamSynchronize(s);
+    destroy_level_textures(tx, nlevels);
     if (rc) return rc;
-    CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
-    CLB_CUDA(cudaStreamSynchronize(s));
+    CLB_CUDA(e1); CLB_CUDA(e2);
     return CLB_OK;
 }
 

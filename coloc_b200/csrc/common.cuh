@@ -80,6 +80,12 @@ struct LevelTable {            // passed by value to kernels (fits in param spac
     const uint8_t* img[CLB_MAX_LEVELS];
 };
 
+struct LevelTex {              // optional point-sampled texture views of the levels (LATCH gather)
+    cudaTextureObject_t t[CLB_MAX_LEVELS];
+};
+int  make_level_textures(const LevelTable& lt, LevelTex& tx);   // levels need 512-B aligned bases, 32-B aligned strides
+void destroy_level_textures(LevelTex& tx, int n);
+
 // match.cu
 size_t match_scratch_bytes(int nQ, int nT);
 int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t t_base,
@@ -107,7 +113,7 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s);
 // latch.cu
 int launch_describe(const LevelTable& lt, const clb_keypoint* d_kps, int n, const int* d_n, int cap,
-                    uint64_t* d_desc, cudaStream_t s);
+                    uint64_t* d_desc, cudaStream_t s, const LevelTex* tex = nullptr);
 int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t s);
 int latch_init();   // uploads the triplet table
 // microbench.cu
