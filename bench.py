@@ -185,6 +185,77 @@ def c2_extra(clb, torch, synth):
     return res
 
 
+def c2_cpu_baseline(O, synth):
+    """cpu_baseline leg for config 2: the same 1280x720 frame through the CPU path of BASELINE.md section 3 on the
+    box's host cores -- resize + LATCH are the oracle restatements (OpenMP; the reference has no CPU LATCH), FAST+NMS is
+    the reference's own KFAST<true,true> (std::async bands) when oracle/_ref is built, orientation is the restatement."""
+    w, h = 1280, 720
+    a, _, _ = synth.frame_pair(w, h, 0)
+    have_ref = O.ref_cpu() is not None
+    best = None
+    for _ in range(2):
+        t0 = time.perf_counter(); pyr = O.pyramid(a); t1 = time.perf_counter()
+        if have_ref:
+            for lv in pyr:
+                O.ref_kfast(lv, 40, multithread=True)
+        t2 = time.perf_counter()
+        kps, desc, _p = O.detect_describe(a, thresh=40, cap=400000, want_pyramid=True); t3 = time.perf_counter()
+        O.latch_describe(pyr, kps); t4 = time.perf_counter()
+        port_detect = max(0.0, (t3 - t2) - (t1 - t0) - (t4 - t3))      # FAST+NMS+angle share of the port's full pass
+        st = {"resize": t1 - t0, "fast_nms": (t2 - t1) if have_ref else port_detect, "describe": t4 - t3, "port_full_pass": t3 - t2}
+        tot = st["resize"] + st["fast_nms"] + st["describe"]
+        if best is None or tot < best[0]:
+            best = (tot, st, len(kps))
+    tot, st, n = best
+    return {"frame": "1280x720, 8 levels x1.2, FAST thresh 40", "keypoints": int(n), "frames_per_s": 1.0 / tot,
+            "stage_ms": {k: 1e3 * v for k, v in st.items()}, "cores": os.cpu_count(),
+            "kind": {"resize": "port", "fast_nms": "reference" if have_ref else "port", "describe": "port"},
+            "note": "fast_nms excludes the orientation pass when the reference KFAST is timed (featureAngle is <2 % of it)"}
+
+
+def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
+    """throughput mode (clb_stream_*): `nframes` frames of w x h from pinned host memory, up to 3 in flight; per frame the
+    keypoints + descriptors come back to pinned host memory and, with_match, frame k is matched against frame k-1 on the
+    device (descriptors never leave it) and the match list is read back.  Wall-clock frames/s, everything included."""
+    pins = []
+    for i in range(distinct):
+        t = torch.empty((h, w), dtype=torch.uint8).pin_memory(); t.numpy()[:] = synth.textured_frame(w, h, 1000 + i); pins.append(t)
+    maxkp = 400000 if w * h > 2000000 else 120000
+    fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp)
+    m = clb.Matcher(maxkp=maxkp) if with_match else None
+    out = torch.zeros(maxkp, dtype=torch.int32, device="cuda") if with_match else None
+    st = torch.cuda.current_stream().cuda_stream
+    res = {}
+
+    def run(n):
+        sub = done = 0; nk = 0; ncmp = 0; nm = 0
+        prev = None
+        while done < n:
+            while sub < n and fs.in_flight() < 3:
+                fs.submit(pins[sub % distinct].numpy(), tag=sub); sub += 1
+            tag, k, d, dk, dd, cnt = fs.next(copy=False)
+            nk += cnt
+            if with_match and prev is not None and cnt > 0 and prev[1] > 0:
+                m.match_dev(dd, cnt, prev[0], prev[1], 40, out, stream=st)
+                nm += int((out[:cnt].cpu() >= 0).sum()); ncmp += cnt * prev[1]
+            prev = (dd, cnt)
+            done += 1
+        return nk, ncmp, nm
+
+    run(min(8, nframes))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); nk, ncmp, nm = run(nframes); torch.cuda.synchronize(); dt = time.perf_counter() - t0
+    res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": 3, "keypoints_per_frame": nk / nframes,
+           "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt,
+           "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0)}
+    if with_match:
+        res["match_cmp_per_s"] = ncmp / dt; res["matches_per_frame"] = nm / max(1, nframes - 1)
+    fs.close()
+    if m:
+        m.close()
+    return res
+
+
 def measured_peaks():
     """driver-written roofline denominators (MEASURED_PEAKS.json at the repo root), {} if absent"""
     try:
@@ -344,9 +415,19 @@ def run_ours(args, rank, world, local_rank):
         line["cpu_baseline"] = {"value": nq_s * float(NT) / dt, "unit": "comparisons/s", "cores": os.cpu_count(), "kind": kind,
                                 "sample": f"{nq_s} of {NQ} queries x {NT} DB rows, one pass ({dt:.1f} s)"}
         try:
+            line["cpu_baseline"]["c2_detect_describe"] = c2_cpu_baseline(O, synth)
+        except Exception as e:
+            line["cpu_baseline"]["c2_detect_describe_error"] = repr(e)
+        try:
             line["extra"] = {"c2_pipeline": c2_extra(clb, torch, synth)}
         except Exception as e:   # the headline number must still print
             line["extra"] = {"c2_pipeline_error": repr(e)}
+        for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
+                       ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
+            try:
+                line["extra"][key] = stream_extra(clb, torch, synth, *a)
+            except Exception as e:
+                line["extra"][key + "_error"] = repr(e)
     print(json.dumps(line), flush=True)
 
 

@@ -271,3 +271,57 @@ class Matcher:
     def merge_partials_dev(self, d_parts, nparts, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
         _check(lib().clb_merge_partials_dev(self._h, _dptr(d_parts), int(nparts), int(nQ), int(threshold),
                                             _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))
+
+
+class FrameStream:
+    """throughput mode of the detector (clb_stream_*): up to `depth` frames in flight, results in submission order.
+    Same output as Detector.detect_and_describe, frame for frame."""
+
+    def __init__(self, width, height, depth=3, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0):
+        self.opts = DetectorOpts(scale_factor, scale_levels, width, height, maxkp, thresh)
+        self.depth = int(depth)
+        self._h = C.c_void_p()
+        L = lib()
+        L.clb_stream_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64]
+        _check(L.clb_stream_create(C.byref(self.opts), int(device), self.depth, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().clb_stream_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def in_flight(self):
+        return int(lib().clb_stream_in_flight(self._h))
+
+    def submit(self, img, tag=0):
+        """img: contiguous-row uint8 numpy array (pinned or pageable) or (ptr, w, h, stride)"""
+        if isinstance(img, tuple):
+            ptr, w, h, stride = img
+        else:
+            assert img.dtype == np.uint8 and img.strides[1] == 1
+            h, w = img.shape
+            ptr, stride = img.ctypes.data, img.strides[0]
+        _check(lib().clb_stream_submit(self._h, C.c_void_p(ptr), int(w), int(h), int(stride), C.c_uint64(int(tag))))
+
+    def next(self, copy=True, want_host=True):
+        """-> (tag, kps, desc, d_kps_ptr, d_desc_ptr); kps/desc are views of pinned memory unless copy=True"""
+        tag = C.c_uint64(0); n = C.c_int(0)
+        pk = C.c_void_p(); pd = C.c_void_p(); dk = C.c_void_p(); dd = C.c_void_p()
+        _check(lib().clb_stream_next(self._h, C.byref(tag), C.byref(pk) if want_host else None, C.byref(pd) if want_host else None,
+                                     C.byref(dk), C.byref(dd), C.byref(n)))
+        kps = desc = None
+        if want_host:
+            if n.value > 0:
+                kps = np.ctypeslib.as_array(C.cast(pk, C.POINTER(C.c_uint8)), shape=(n.value * 20,)).view(KP_DTYPE)
+                desc = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_uint64)), shape=(n.value, 8))
+                if copy:
+                    kps, desc = kps.copy(), desc.copy()
+            else:
+                kps, desc = np.zeros(0, KP_DTYPE), np.zeros((0, 8), np.uint64)
+        return int(tag.value), kps, desc, dk.value, dd.value, int(n.value)

@@ -353,3 +353,119 @@ int clb_sincos(clb_detector* d, const float* angles, int n, float* sin_out, floa
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------ frame stream
+// `depth` independent detector contexts used round-robin; see include/coloc_b200.h.
+struct clb_stream_slot {
+    clb_detector* det;
+    uint8_t* h_img; size_t h_img_cap;      // pinned staging for pageable inputs
+    clb_keypoint* h_kps; uint64_t* h_desc; // pinned results (maxkp entries)
+    uint64_t tag;
+};
+struct clb_stream {
+    int depth, head, tail, inflight, device;
+    clb_detector_opts o;
+    clb_stream_slot* slots;
+};
+
+extern "C" {
+
+void clb_stream_destroy(clb_stream* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    for (int i = 0; s->slots && i < s->depth; ++i) {
+        if (s->slots[i].det) { cudaStreamSynchronize(s->slots[i].det->stream); clb_detector_destroy(s->slots[i].det); }
+        if (s->slots[i].h_img) cudaFreeHost(s->slots[i].h_img);
+        if (s->slots[i].h_kps) cudaFreeHost(s->slots[i].h_kps);
+        if (s->slots[i].h_desc) cudaFreeHost(s->slots[i].h_desc);
+    }
+    delete[] s->slots;
+    delete s;
+}
+
+int clb_stream_create(const clb_detector_opts* opts, int device, int depth, clb_stream** out) {
+    if (!opts || !out || depth < 1 || depth > 16) { snprintf(g_err, sizeof(g_err), "bad stream options (depth 1..16)"); return CLB_EINVAL; }
+    clb_stream* s = new (std::nothrow) clb_stream();
+    if (!s) return CLB_ENOMEM;
+    s->depth = depth; s->head = s->tail = s->inflight = 0; s->device = device; s->o = *opts;
+    s->slots = new (std::nothrow) clb_stream_slot[depth]();
+    if (!s->slots) { delete s; return CLB_ENOMEM; }
+    for (int i = 0; i < depth; ++i) {
+        int rc = clb_detector_create(opts, device, &s->slots[i].det);
+        cudaError_t e = cudaSuccess;
+        if (!rc) e = cudaMallocHost(&s->slots[i].h_kps, (size_t)opts->maxkp * sizeof(clb_keypoint));
+        if (!rc && e == cudaSuccess) e = cudaMallocHost(&s->slots[i].h_desc, (size_t)opts->maxkp * 64);
+        if (!rc && e != cudaSuccess) rc = set_cuda_error(e, "stream pinned allocation", __FILE__, __LINE__);
+        if (rc) { clb_stream_destroy(s); return rc; }
+    }
+    *out = s;
+    return CLB_OK;
+}
+
+int clb_stream_in_flight(const clb_stream* s) { return s ? s->inflight : 0; }
+
+int clb_stream_submit(clb_stream* s, const uint8_t* gray, int w, int h, int stride, uint64_t tag) {
+    if (!s || !gray) return CLB_EINVAL;
+    if (s->inflight == s->depth) { snprintf(g_err, sizeof(g_err), "%d frames already in flight", s->depth); return CLB_ECAPACITY; }
+    clb_stream_slot& sl = s->slots[s->tail];
+    clb_detector* d = sl.det;
+    int rc = check_frame(d, w, h, stride);
+    if (rc) return rc;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = d->stream;
+    LevelTable lt;
+    make_table(d, w, h, lt);
+    // pinned input: DMA straight from the caller's buffer; pageable input: stage it so the copy is truly asynchronous
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, gray) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    const uint8_t* src = gray; int src_stride = stride;
+    if (!pinned) {
+        const size_t need = (size_t)w * h;
+        if (need > sl.h_img_cap) {
+            if (sl.h_img) cudaFreeHost(sl.h_img);
+            sl.h_img = nullptr; sl.h_img_cap = 0;
+            CLB_CUDA(cudaMallocHost(&sl.h_img, need));
+            sl.h_img_cap = need;
+        }
+        for (int y = 0; y < h; ++y) memcpy(sl.h_img + (size_t)y * w, gray + (size_t)y * stride, (size_t)w);
+        src = sl.h_img; src_stride = w;
+    }
+    CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], src, src_stride, w, h, cudaMemcpyHostToDevice, st));
+    rc = run_pipeline(d, lt, st);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d->misc.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    sl.tag = tag;
+    s->tail = (s->tail + 1) % s->depth;
+    ++s->inflight;
+    return CLB_OK;
+}
+
+int clb_stream_next(clb_stream* s, uint64_t* tag_out, const clb_keypoint** kps_out, const uint64_t** desc_out,
+                    const clb_keypoint** d_kps_out, const uint64_t** d_desc_out, int* n_out) {
+    if (!s || !n_out) return CLB_EINVAL;
+    if (s->inflight == 0) { snprintf(g_err, sizeof(g_err), "no frame in flight"); return CLB_EINVAL; }
+    clb_stream_slot& sl = s->slots[s->head];
+    clb_detector* d = sl.det;
+    s->head = (s->head + 1) % s->depth;
+    --s->inflight;
+    CLB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = d->stream;
+    CLB_CUDA(cudaStreamSynchronize(st));
+    const int n = *d->h_total;
+    *n_out = n;
+    if (tag_out) *tag_out = sl.tag;
+    if (n > d->o.maxkp) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed maxkp %d", n, d->o.maxkp); return CLB_ECAPACITY; }
+    if (n > 0 && (kps_out || desc_out)) {
+        if (kps_out) CLB_CUDA(cudaMemcpyAsync(sl.h_kps, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, st));
+        if (desc_out) CLB_CUDA(cudaMemcpyAsync(sl.h_desc, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, st));
+        CLB_CUDA(cudaStreamSynchronize(st));
+    }
+    if (kps_out) *kps_out = sl.h_kps;
+    if (desc_out) *desc_out = sl.h_desc;
+    if (d_kps_out) *d_kps_out = d->kps.as<clb_keypoint>();
+    if (d_desc_out) *d_desc_out = d->desc.as<uint64_t>();
+    return CLB_OK;
+}
+
+}  // extern "C"

@@ -106,6 +106,25 @@ int  clb_describe(clb_detector* d, const uint8_t* const* levels, const int32_t* 
 /* device sin/cos used by the describe kernel (CLATCH.cu:161), for ulp-level parity tests */
 int  clb_sincos(clb_detector* d, const float* angles, int n, float* sin_out, float* cos_out);
 
+/* ---------------------------------------------------------------- frame stream ----------- */
+/* Throughput mode for a stream of frames (BASELINE config 5).  The reference calls
+ * detectAndDescribe once per frame and blocks (GPUDetector.hpp:290); a stream keeps `depth` frames in
+ * flight, each on its own CUDA stream with its own pyramid / keypoint / descriptor buffers and pinned
+ * result staging, so the H2D copy of frame k+1 and the D2H copy of frame k-1 overlap the kernels of
+ * frame k.  Results are bit-identical to clb_detect_describe and come back in submission order. */
+typedef struct clb_stream clb_stream;
+int  clb_stream_create(const clb_detector_opts* opts, int device, int depth, clb_stream** out);
+void clb_stream_destroy(clb_stream* s);
+/* enqueue one frame (HOST pointer; pinned memory is copied from directly, pageable memory is staged).
+ * Returns CLB_ECAPACITY when `depth` frames are already in flight (call clb_stream_next first). */
+int  clb_stream_submit(clb_stream* s, const uint8_t* gray, int w, int h, int stride, uint64_t tag);
+/* wait for the OLDEST frame in flight.  kps_out / desc_out point into pinned HOST memory, d_kps_out /
+ * d_desc_out at the DEVICE copies (any of them may be NULL); all stay valid until `depth` - 1 further
+ * frames have been submitted.  CLB_EINVAL when nothing is in flight. */
+int  clb_stream_next(clb_stream* s, uint64_t* tag_out, const clb_keypoint** kps_out, const uint64_t** desc_out,
+                     const clb_keypoint** d_kps_out, const uint64_t** d_desc_out, int* n_out);
+int  clb_stream_in_flight(const clb_stream* s);
+
 /* ---------------------------------------------------------------- matcher ---------------- */
 /* GPUMatcher::GPUMatcher(MatcherOptions)  include/coloc/GPUMatcher.hpp:70-95 */
 int  clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** out);

@@ -330,3 +330,45 @@ def test_pair_pipeline_recovers_homography(clb, oracle):
     err = np.hypot(pb[0] - kb["x"][match[idx]] * sb, pb[1] - kb["y"][match[idx]] * sb)
     assert np.median(err) < 3.0 and (err < 6).mean() > 0.8
     det.close(); m.close()
+
+
+# ------------------------------------------------------------------ frame stream (throughput mode)
+@pytest.mark.parametrize("depth", [1, 3])
+def test_frame_stream_equals_single_frame_calls(clb, depth):
+    """clb_stream_*: frames of different content and size, pinned and pageable, more frames than ring slots;
+    every result bit-identical to clb_detect_describe and returned in submission order."""
+    import torch
+    sizes = [(640, 480), (333, 251), (640, 480), (512, 384), (640, 480), (64, 48), (640, 480)]
+    frames = [synth.textured_frame(w, h, 50 + i) for i, (w, h) in enumerate(sizes)]
+    det = clb.Detector(640, 480, maxkp=30000, thresh=30)
+    want = []
+    for f in frames:
+        k, d = det.detect_and_describe(f)
+        want.append((k.copy(), d.copy()))
+    det.close()
+    fs = clb.FrameStream(640, 480, depth=depth, maxkp=30000, thresh=30)
+    pinned = []
+    got = {}
+    nxt = 0
+    for i, f in enumerate(frames):
+        if i % 2 == 0:                                        # every other frame from pinned memory
+            t = torch.empty(f.shape, dtype=torch.uint8).pin_memory(); t.numpy()[:] = f; pinned.append(t); f = t.numpy()
+        if fs.in_flight() == depth:
+            tag, k, d, dk, dd, n = fs.next()
+            assert tag == nxt and dk and dd; got[tag] = (k, d); nxt += 1
+        fs.submit(f, tag=i)
+    with pytest.raises(clb.ClbError):                          # ring full -> loud error, nothing dropped
+        while True:
+            fs.submit(frames[0], tag=99)
+    while fs.in_flight():
+        tag, k, d, dk, dd, n = fs.next()
+        if tag == 99:
+            continue
+        assert tag == nxt; got[tag] = (k, d); nxt += 1
+    assert nxt == len(frames)
+    for i, (k, d) in enumerate(want):
+        assert len(k) > 0 or sizes[i][0] < 100
+        assert np.array_equal(got[i][0].view(np.uint8), k.view(np.uint8)) and np.array_equal(got[i][1], d), i
+    with pytest.raises(clb.ClbError):
+        fs.next()
+    fs.close()
