@@ -148,7 +148,7 @@ def run_reference(args, rank, world):
 def c2_extra(clb, torch, synth):
     """config 2 (1280x720 pair, 8 levels): detect+describe per frame and the pair match, device-timed."""
     w, h = 1280, 720
-    a, b, _ = synth.frame_pair(w, h, 0)
+    a, b, _ = synth.config_frame_pair(w, h, 0)
     det = clb.Detector(w, h, maxkp=120000)
     clb.set_timing(True)
     res = {}
@@ -190,7 +190,7 @@ def c2_cpu_baseline(O, synth):
     box's host cores -- resize + LATCH are the oracle restatements (OpenMP; the reference has no CPU LATCH), FAST+NMS is
     the reference's own KFAST<true,true> (std::async bands) when oracle/_ref is built, orientation is the restatement."""
     w, h = 1280, 720
-    a, _, _ = synth.frame_pair(w, h, 0)
+    a = synth.config_frame(w, h, 0)
     have_ref = O.ref_cpu() is not None
     best = None
     for _ in range(2):
@@ -218,8 +218,9 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
     keypoints + descriptors come back to pinned host memory and, with_match, frame k is matched against frame k-1 on the
     device (descriptors never leave it) and the match list is read back.  Wall-clock frames/s, everything included."""
     pins = []
+    views, _ = synth.config_views(w, h, distinct)            # consecutive frames see the same scene (matches exist)
     for i in range(distinct):
-        t = torch.empty((h, w), dtype=torch.uint8).pin_memory(); t.numpy()[:] = synth.textured_frame(w, h, 1000 + i); pins.append(t)
+        t = torch.empty((h, w), dtype=torch.uint8).pin_memory(); t.numpy()[:] = views[i]; pins.append(t)
     maxkp = 400000 if w * h > 2000000 else 120000
     fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp)
     m = clb.Matcher(maxkp=maxkp) if with_match else None
@@ -254,6 +255,73 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
     if m:
         m.close()
     return res
+
+
+def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
+    """config 3: 4 vehicles' 1280x720 views of one scene (random homographies), all 12 ordered inter-vehicle pairs matched; the flattened (pair, query row)
+    list is cut into `world` contiguous slices (shard.pair_row_plan), no exchange inside the data path, one all-gather of
+    the int32 match lists at the end of the step.  Every rank detects + describes the 4 frames itself (0.2 ms each)."""
+    w, h = 1280, 720
+    ok = 1
+    try:
+        det = clb.Detector(w, h, maxkp=120000, device=dev.index)
+        descs = []
+        views, _ = synth.config_views(w, h, 4)
+        for k in range(4):
+            _, d = det.detect_and_describe(views[k])
+            descs.append(torch.from_numpy(d.copy().view(np.int64)).to(dev))
+        det.close()
+        counts = [int(d.shape[0]) for d in descs]
+        pairs = shard.ordered_pairs(4)
+        plan = shard.pair_row_plan(pairs, counts, rank, world)
+        total_rows = sum(counts[q] for q, _ in pairs)
+        lo, hi = shard.shard_range(total_rows, rank, world)
+        slice_max = (total_rows + world - 1) // world
+        mine = torch.full((slice_max,), -2, dtype=torch.int32, device=dev)
+        allm = torch.empty((world, slice_max), dtype=torch.int32, device=dev)
+        m = clb.Matcher(maxkp=max(counts) + 16, device=dev.index)
+        st = torch.cuda.current_stream().cuda_stream
+    except Exception as e:
+        ok = 0; err = repr(e)
+    flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 0:
+        return {"error": err if not ok else "another rank failed"}
+
+    def step():
+        off = 0
+        for p, a, b in plan:
+            qi, ti = pairs[p]
+            m.match_dev(descs[qi][a:b], b - a, descs[ti], counts[ti], 40, mine[off:off + (b - a)], stream=st)
+            off += b - a
+        if world > 1:
+            dist.all_gather_into_tensor(allm.view(-1), mine)
+        else:
+            allm[0].copy_(mine)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record(); torch.cuda.synchronize()
+    tm = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms = float(tm.item()) / steps
+    cmp_step = float(sum(counts[q] * counts[t] for q, t in pairs))
+    got = allm.cpu().numpy()
+    matched = int(sum((got[r][:shard.shard_range(total_rows, r, world)[1] - shard.shard_range(total_rows, r, world)[0]] >= 0).sum()
+                      for r in range(world)))
+    m.close()
+    return {"frames": 4, "pairs": 12, "keypoints": counts, "query_rows": total_rows, "comparisons_per_step": cmp_step,
+            "ms_per_step": ms, "comparisons_per_s": cmp_step / (ms * 1e-3), "matched_rows": matched,
+            "parallelism": f"query rows x{world}, all-gather of int32 match lists"}
 
 
 def measured_peaks():
@@ -350,6 +418,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     tot_ms, e2e_ms = tm.tolist()
+    c3 = c3_extra(clb, torch, dist, synth, shard, rank, world, dev)      # collective: every rank takes part
     if rank != 0:
         return
     cmp_per_step = float(NQ) * float(NT)
@@ -397,6 +466,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
+            "extra": {"c3_pairs": c3},
             }
     if world == 1:
         # CPU baseline beside it (bounded sample) + config-2 stage numbers
@@ -419,9 +489,9 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:
             line["cpu_baseline"]["c2_detect_describe_error"] = repr(e)
         try:
-            line["extra"] = {"c2_pipeline": c2_extra(clb, torch, synth)}
+            line["extra"]["c2_pipeline"] = c2_extra(clb, torch, synth)
         except Exception as e:   # the headline number must still print
-            line["extra"] = {"c2_pipeline_error": repr(e)}
+            line["extra"]["c2_pipeline_error"] = repr(e)
         for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
                        ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
             try:

@@ -22,8 +22,10 @@ def _value_noise(rng, h, w, octaves=6):
     return img / tot
 
 
-def textured_frame(w, h, seed, shapes=None):
-    """uint8 frame: multi-octave value noise + random filled rectangles and discs (corners for FAST)."""
+def textured_frame(w, h, seed, shapes=None, max_size=None):
+    """uint8 frame: multi-octave value noise + random filled rectangles and discs (corners for FAST).
+    `shapes` / `max_size` (pixels) set the corner density: the defaults give ~9k keypoints at 1280x720 (threshold 40),
+    bench.py passes denser settings to reach the keypoint counts BASELINE.json's configs name."""
     rng = np.random.default_rng(seed)
     img = _value_noise(rng, h, w) * 255.0
     n = shapes if shapes is not None else max(40, (w * h) // 600)
@@ -32,16 +34,44 @@ def textured_frame(w, h, seed, shapes=None):
         val = float(rng.integers(0, 256))
         if rng.random() < 0.6:
             x0 = int(rng.integers(0, w)); y0 = int(rng.integers(0, h))
-            rw = int(rng.integers(4, max(5, w // 12))); rh = int(rng.integers(4, max(5, h // 12)))
+            rw = int(rng.integers(4, max(5, max_size or w // 12))); rh = int(rng.integers(4, max(5, max_size or h // 12)))
             img[y0:y0 + rh, x0:x0 + rw] = 0.35 * img[y0:y0 + rh, x0:x0 + rw] + 0.65 * val
         else:
-            cx = int(rng.integers(0, w)); cy = int(rng.integers(0, h)); r = int(rng.integers(3, max(4, h // 20)))
+            cx = int(rng.integers(0, w)); cy = int(rng.integers(0, h)); r = int(rng.integers(3, max(4, (max_size // 2) if max_size else h // 20)))
             ya, yb = max(0, cy - r), min(h, cy + r + 1); xa, xb = max(0, cx - r), min(w, cx + r + 1)
             yy, xx = np.mgrid[ya:yb, xa:xb]
             m = (yy - cy) ** 2 + (xx - cx) ** 2 <= r * r
             sub = img[ya:yb, xa:xb]
             sub[m] = 0.35 * sub[m] + 0.65 * val
     return np.clip(img + 0.5, 0, 255).astype(np.uint8)
+
+
+# corner densities that reach the keypoint counts BASELINE.json's configs name at FAST threshold 40
+# (C1 640x480 ~5k, C2/C3 1280x720 ~20k, C5 3840x2160 ~50k); (shapes, max_size) for textured_frame
+CONFIG_DENSITY = {(640, 480): (650, 40), (1280, 720): (3900, 48), (3840, 2160): (4900, 64)}
+
+
+def config_frame(w, h, k=0):
+    """frame k of a BASELINE config: seed 1000+k, density from CONFIG_DENSITY (default density for other sizes)."""
+    sh, ms = CONFIG_DENSITY.get((w, h), (None, None))
+    return textured_frame(w, h, 1000 + k, sh, ms)
+
+
+def config_frame_pair(w, h, k=0):
+    a = config_frame(w, h, k)
+    H = random_homography(w, h, 2000 + k)
+    return a, warp_homography(a, H), H
+
+
+def config_views(w, h, n, k=0):
+    """n views of the same scene (config 3: n vehicles looking at one area): view 0 is config_frame(w, h, k), view i > 0 is
+    its warp by the random homography of seed 2000 + 16 k + i.  Returns (views, homographies) with H[0] = identity."""
+    base = config_frame(w, h, k)
+    views, Hs = [base], [np.eye(3)]
+    for i in range(1, n):
+        H = random_homography(w, h, 2000 + 16 * k + i)
+        views.append(warp_homography(base, H)); Hs.append(H)
+    return views, Hs
 
 
 def random_homography(w, h, seed):
