@@ -15,6 +15,7 @@ struct clb_matcher {
     DevBuf qx, tx, mapx;              // +-1 E4M3 expansions for the tensor-core path (match_tc.cu)
     int n_map;
     bool mapx_valid;
+    int mapx_ver;                     // kernel version the cached map expansion was made for
 };
 
 // Expand the operands when the tensor-core path applies; *Qx / *Tx stay NULL for the POPC path.
@@ -32,11 +33,11 @@ static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
         *Qx = m->qx.p;
     }
     if (map) {
-        if (!m->mapx_valid) {
+        if (!m->mapx_valid || m->mapx_ver != tc_version()) {
             CLB_CUDA(m->mapx.reserve(tb));
             rc = launch_expand(dT, nT, tb, m->mapx.p, s);
             if (rc) return rc;
-            m->mapx_valid = true;
+            m->mapx_valid = true; m->mapx_ver = tc_version();
         }
         *Tx = m->mapx.p;
     } else {
@@ -81,7 +82,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     CLB_CUDA(cudaSetDevice(device));
     clb_matcher* m = new (std::nothrow) clb_matcher();
     if (!m) return CLB_ENOMEM;
-    m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->stream = nullptr;
+    m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->mapx_ver = 0; m->stream = nullptr;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);

@@ -101,6 +101,7 @@ size_t tc_q_bytes(int nQ);
 size_t tc_t_bytes(int nT);
 int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s);
 void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, int* tpc_out);
+int  tc_version();
 bool tc_needs_qx();      // v1 kernel (queries staged in shared memory) wants the expanded query image too
 int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s);

@@ -346,10 +346,10 @@ static constexpr int TC2_SMEM_B = TC2_STAGES * TC_KB_BYTES;          // 229376
 static constexpr int TC2_SMEM_BAR = 512;
 static constexpr int TC2_SMEM_TOTAL = TC2_SMEM_B + TC2_SMEM_BAR + 1024;
 
-__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t accumulate, uint32_t idesc = TC_IDESC) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], [%1], %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(TC_IDESC), "r"(accumulate) : "memory");
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32]) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
@@ -432,6 +432,11 @@ match_tc2_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
                         const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
                         const uint32_t a0 = tmem + (uint32_t)(m * TC_TILE + kb * 32);
                         const uint32_t d0 = tmem + (uint32_t)(256 + m * TC_TILE);
+                        if (dbg == 6) {      // timing experiment: same MACs as 2 x N=256 instructions (results are garbage)
+                            for (int k = 0; k < 2; ++k)
+                                tc_mma_ts(tmem + 256u, a0 + (uint32_t)(k * 8), (desc_hi | (uint64_t)((sB & 0x3FFFFu) >> 4)) + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0),
+                                          (1u << 4) | (32u << 17) | (8u << 24));
+                        } else
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             tc_mma_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0));
@@ -497,6 +502,183 @@ match_tc2_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
     }
 }
 
+// ---- v3: E2M1 (fp4) operands, kind::mxf4 block-scaled MMA at twice the fp8 rate ------------------------
+// +-1 is exact in E2M1 too (0x2 / 0xA), and kind::mxf4 multiplies K = 64 elements per instruction at 16 384 MAC/clk/SM:
+// 32 comparisons per clock per SM.  The block scales the instruction insists on are UE8M0 bytes; 0x7F = 2^0, so a TMEM
+// region filled with 0x7F7F7F7F serves as scale factor A and B whatever the layout rules say.  Operands are packed two
+// per byte: a row is 256 B = 2 K-blocks of 128 B, a 128-row tile 32 KB (half the L2 -> smem traffic per comparison).
+// Both operands come from shared memory (SS mode); the two accumulators alternate as in v2.
+static constexpr int TC3_KB = 2;                                    // K-blocks (128 B = 256 E2M1) per row
+static constexpr int TC3_TILE_BYTES = TC3_KB * TC_KB_BYTES;         // 32 KB
+static constexpr int TC3_SMEM_A = TC_QTILES * TC3_TILE_BYTES;       // 64 KB
+static constexpr int TC3_STAGES = 10;
+static constexpr int TC3_SMEM_B = TC3_STAGES * TC_KB_BYTES;         // 160 KB
+static constexpr int TC3_SMEM_TOTAL = TC3_SMEM_A + TC3_SMEM_B + TC2_SMEM_BAR + 1024;
+// block-scaled instruction descriptor: A = B = E2M1 (MXF4Format 1) at bits 7 / 10, N>>3 at 17, scale format UE8M0 at 23, M>>4 at 24
+static constexpr uint32_t TC3_IDESC = (1u << 7) | (1u << 10) | ((uint32_t)(TC_TILE >> 3) << 17) | (1u << 23) | ((uint32_t)(TC_TILE >> 4) << 24);
+
+__device__ __forceinline__ void tc_mma_mxf4(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t accumulate, uint32_t sfa, uint32_t sfb) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(TC3_IDESC), "r"(accumulate), "r"(sfa), "r"(sfb) : "memory");
+}
+
+// 8 descriptor bits -> 8 E2M1 nibbles (one 32-bit word): bit 1 -> 0x2 (+1.0), bit 0 -> 0xA (-1.0); bit i lands in nibble i
+__device__ __forceinline__ uint32_t tc_nib4(uint32_t x) {
+    uint32_t y = (x | (x << 12)) & 0x000F000Fu;
+    y = (y | (y << 6)) & 0x03030303u;
+    y = (y | (y << 3)) & 0x11111111u;
+    return 0xAAAAAAAAu ^ (y << 3);
+}
+// One thread per 16-byte output chunk (= one packed 32-bit word of the row), output order.
+// Layout: [tile of 128 rows][2 K-blocks][128 rows][128 B], 16-B chunk c of row r at chunk c ^ (r & 7).
+__global__ void __launch_bounds__(256)
+expand4_kernel(const uint32_t* __restrict__ rows, int n, size_t n_chunks16, uint4* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_chunks16) return;
+    const int cpos = (int)(i & 7), r = (int)((i >> 3) & 127), kb = (int)((i >> 10) & 1);
+    const size_t tile = i >> 11;
+    const int c = cpos ^ (r & 7);
+    const size_t row = tile * TC_TILE + r;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);                        // E2M1 0x0 = +0.0 for the padding rows
+    if (row < (size_t)n) {
+        const uint32_t w = __ldg(rows + row * 16 + kb * 8 + c);
+        v.x = tc_nib4(w & 255u); v.y = tc_nib4((w >> 8) & 255u); v.z = tc_nib4((w >> 16) & 255u); v.w = tc_nib4(w >> 24);
+    }
+    out[i] = v;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                 uint2* __restrict__ partial, int dbg) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    const uint32_t sA = base, sB = base + TC3_SMEM_A, sBar = sB + TC3_SMEM_B;
+    const uint32_t bar_full = sBar, bar_empty = sBar + 8 * TC3_STAGES, bar_a = sBar + 16 * TC3_STAGES;
+    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 16, bar_sf = bar_tempty + 16, tmem_slot = bar_sf + 8;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+
+    if (tid == 0) {
+        for (int s = 0; s < TC3_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
+        tc_mbar_init(bar_a, 1);
+        tc_mbar_init(bar_sf, TC_EPI_WARPS / 2);
+        for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC_EPI_WARPS / 2); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+    // TMEM map: columns 0-127 / 128-255 accumulators D_0 / D_1, columns 256-319 scale factors (all 1.0)
+    const uint32_t tm_sf = tmem + 256u;
+
+    if (warp == 0) {
+        // ===== producer =====
+        const uint8_t* qsrc = Qx + (size_t)blockIdx.x * TC3_SMEM_A;
+        if (tc_elect_one()) {
+            tc_mbar_expect_tx(bar_a, TC3_SMEM_A);
+            for (int i = 0; i < TC_QTILES * TC3_KB; ++i)
+                tc_bulk_load(sA + i * TC_KB_BYTES, qsrc + (size_t)i * TC_KB_BYTES, TC_KB_BYTES, bar_a);
+        }
+        __syncwarp();
+        const uint8_t* tsrc = Tx + (size_t)tile0 * TC3_TILE_BYTES;
+        const int nit = ntiles * TC3_KB;
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC3_STAGES;
+            tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC3_STAGES) & 1) ^ 1));
+            if (tc_elect_one()) {
+                tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
+                tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        tc_mbar_wait(bar_a, 0);
+        tc_mbar_wait(bar_sf, 0);
+        tc_fence_after();
+        const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        for (int j = 0; j < ntiles; ++j) {
+#pragma unroll
+            for (int m = 0; m < TC_QTILES; ++m) {
+                tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
+                tc_fence_after();
+#pragma unroll
+                for (int kb = 0; kb < TC3_KB; ++kb) {
+                    const int it = j * TC3_KB + kb;
+                    const int s = it % TC3_STAGES;
+                    if (m == 0) {
+                        tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC3_STAGES) & 1));
+                        tc_fence_after();
+                    }
+                    if (tc_elect_one()) {
+                        const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                        const uint64_t a0 = desc_hi | (uint64_t)(((sA + m * TC3_TILE_BYTES + kb * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                        const uint32_t d0 = tmem + (uint32_t)(m * TC_TILE);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            tc_mma_mxf4(d0, a0 + (uint64_t)(k * 2), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0), tm_sf, tm_sf + 32u);
+                        if (m == TC_QTILES - 1) tc_commit(bar_empty + 8 * s);
+                        if (kb == TC3_KB - 1) tc_commit(bar_tfull + 8 * m);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===== epilogue warps =====
+        const int quarter = warp & 3;
+        const int m = (warp - 2) >> 2;
+        const int qi = blockIdx.x * TC_QROWS + m * TC_TILE + quarter * 32 + lane;
+        const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+        if (m == 0) {   // scale-factor region: every byte UE8M0 1.0, all 128 lanes x 64 columns
+            uint32_t r[32];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) r[c] = 0x7F7F7F7Fu;
+            tc_st32(lane_base + 256u, r);
+            tc_st32(lane_base + 288u, r);
+            tc_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc_mbar_arrive(bar_sf);
+        }
+        const uint32_t tbase = lane_base + (uint32_t)(m * TC_TILE);
+        TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
+        const int full_tiles = chunk_rows / TC_TILE;
+        for (int j = 0; j < ntiles; ++j) {
+            tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
+            tc_fence_after();
+            if (dbg == 1) {
+                tc_fence_before(); __syncwarp();
+                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                continue;
+            }
+            if (j < full_tiles) tc_epilogue_tile<false>(tbase, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * m, lane, st);
+            else                tc_epilogue_tile<true>(tbase, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * m, lane, st);
+        }
+        if (qi < nQ) partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(st.best, st.second);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
 // ---- host side --------------------------------------------------------------------------------
 bool tc_wanted(int nQ, int nT) {
     if (g_match_tc == 0 || nQ <= 0 || nT <= 0) return false;
@@ -504,8 +686,9 @@ bool tc_wanted(int nQ, int nT) {
     return (long long)nQ * (long long)nT >= (1ll << 24);    // below that the expansion passes dominate
 }
 
-size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * TC_SMEM_A; }
-size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * TC_TILE_BYTES; }
+int tc_version() { return g_match_tc_ver; }
+size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (g_match_tc_ver == 3 ? TC3_SMEM_A : TC_SMEM_A); }
+size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (g_match_tc_ver == 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
 
 int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s) {
     if (out_bytes == 0) return CLB_OK;
@@ -513,7 +696,10 @@ int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, 
     const size_t blocks = (chunks + 255) / 256;
     if (blocks > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "descriptor set too large to expand"); return CLB_EINVAL; }
     timer("expand").begin(s);
-    expand_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
+    if (g_match_tc_ver == 3)
+        expand4_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
+    else
+        expand_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
     timer("expand").end(s);
     CLB_LAUNCHED();
     return CLB_OK;
@@ -551,7 +737,7 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
     *nchunks_out = total_tiles > 0 ? (total_tiles + *tpc_out - 1) / *tpc_out : 0;
 }
 
-bool tc_needs_qx() { return g_match_tc_ver == 1; }
+bool tc_needs_qx() { return g_match_tc_ver == 1 || g_match_tc_ver == 3; }
 
 int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s) {
@@ -561,11 +747,15 @@ int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const voi
     if (dev < 0 || dev >= 64 || !attr_done[dev]) {
         CLB_CUDA(cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
         CLB_CUDA(cudaFuncSetAttribute(match_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_TOTAL));
+        CLB_CUDA(cudaFuncSetAttribute(match_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC3_SMEM_TOTAL));
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     dim3 grid(qblocks, nchunks);
     timer("match").begin(s);
-    if (g_match_tc_ver == 1 && Qx)
+    if (g_match_tc_ver == 3 && Qx)
+        match_tc3_kernel<<<grid, TC_THREADS, TC3_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
+                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
+    else if (g_match_tc_ver == 1 && Qx)
         match_tc_kernel<<<grid, TC_THREADS, TC_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
                                                               reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
     else
