@@ -440,23 +440,28 @@ def run_ours(args, rank, world, local_rank):
     else:
         peaks = measured_peaks()
         bf16 = peaks.get("bf16_tflops")                        # burst figure: the kernel keeps 1965 MHz (+-1 operands)
-        peak_tf = 2.0 * bf16 if bf16 else 2.0 * 1590.0
+        mult = 4.0 if path >= 3 else 2.0                       # fp4 (kind::mxf4) issues at 4x, fp8 at 2x the bf16 rate
+        peak_tf = mult * bf16 if bf16 else mult * 1590.0
         ach_tf = 1024.0 * cmp_s_kernel / 1e12
         roof = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
-                "traffic": None, "kernel": "clb::match_tc2_kernel" if path == 2 else "clb::match_tc_kernel", "kernel_ms": k_ms,
-                "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (fp8 issues at twice the bf16 rate)" if bf16 else
-                                "2 x 1590 TFLOP/s fallback (B200_PROFILING.md)"),
-                "frac_of_nominal_fp8_4500": ach_tf / 4500.0,
+                "traffic": None, "kernel": {1: "clb::match_tc_kernel", 2: "clb::match_tc2_kernel", 3: "clb::match_tc3_kernel",
+                                            4: "clb::match_tc4_kernel"}[path], "kernel_ms": k_ms,
+                "peak_source": (f"{mult:.0f} x MEASURED_PEAKS.json bf16_tflops (fp8 issues at 2x, fp4 at 4x the bf16 rate; no fp8/fp4 figure is measured)"
+                                if bf16 else f"{mult:.0f} x 1590 TFLOP/s fallback (B200_PROFILING.md)"),
+                "frac_of_nominal": ach_tf / (9000.0 if path >= 3 else 4500.0),
                 "popc_roofline": {"achieved": popc_ach, "peak": pipes["popc_gops"], "unit": "G POPC32/s", "frac": popc_frac,
                                   "note": "north_star's roofline: 16 POPC32 per comparison against the measured POPC pipe; "
                                           "the tensor-core formulation is what lets frac exceed 1"},
-                "note": "hamming = (512 - <q,t>)/2 over +-1 E4M3 operands, tcgen05.mma kind::f8f6f4 M128 N128 K32, fp32 accumulate "
-                        "(exact); 1024 flop per comparison; DB expansion (64 B -> 512 B per row) is inside the step",
+                "note": ("hamming = (512 - <q,t>)/2 over +-1 E2M1 operands, tcgen05.mma kind::mxf4.block_scale (unit scales) M128 N128 K64, "
+                         "fp32 accumulate (exact); 1024 flop per comparison; DB expansion (64 B -> 256 B per row) is inside the step"
+                         if path >= 3 else
+                         "hamming = (512 - <q,t>)/2 over +-1 E4M3 operands, tcgen05.mma kind::f8f6f4 M128 N128 K32, fp32 accumulate "
+                         "(exact); 1024 flop per comparison; DB expansion (64 B -> 512 B per row) is inside the step"),
                 "pipes": pipes}
     line = {"metric": "hamming_512b_comparisons_per_s", "value": value, "unit": "comparisons/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": value / PUBLISHED_CMP_S,
-            "dtype": ("u32 xor/popc" if path == 0 else "e4m3 +-1 operands, f32 accumulate (exact integers)"), "data": "synthetic",
+            "dtype": ("u32 xor/popc" if path == 0 else ("e2m1" if path >= 3 else "e4m3") + " +-1 operands, f32 accumulate (exact integers)"), "data": "synthetic",
             "config": {"workload": "C4 map relocalization: 50k queries x 2M-row DB, 512-bit descriptors, 2-NN + margin test",
                        "nQ": NQ, "nT": NT, "threshold": THRESH, "parallelism": f"db-rows x{world}",
                        "l2": "256 MiB device fill between steps, outside the per-step event pairs",

@@ -112,7 +112,7 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_hs")) { if (value < 0 || value > 3) return CLB_EINVAL; g_match_hs = value; }
     else if (!strcmp(name, "match_chunks")) { if (value < 0) return CLB_EINVAL; g_match_chunks = value; }
     else if (!strcmp(name, "match_tc")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_tc = value; }
-    else if (!strcmp(name, "match_tc_ver")) { if (value < 1 || value > 3) return CLB_EINVAL; g_match_tc_ver = value; }
+    else if (!strcmp(name, "match_tc_ver")) { if (value < 1 || value > 4) return CLB_EINVAL; g_match_tc_ver = value; }
     else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;

@@ -306,7 +306,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
         if ((size_t)nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
         if (nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }
         uint2* part = reinterpret_cast<uint2*>(scratch);
-        g_last_match_path = (g_match_tc_ver != 2 && Qx) ? g_match_tc_ver : 2;
+        g_last_match_path = (g_match_tc_ver == 4 || Qx) ? g_match_tc_ver : 2;
         int rc = launch_match_tc_kernel(dQ, Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
         if (rc) return rc;
         timer("merge").begin(s);

@@ -30,7 +30,7 @@ namespace clb {
 int g_match_tc = -1;        // -1 auto, 0 never, 1 always (clb_set_param "match_tc")
 int g_match_tc_chunks = 0;  // 0 = heuristic
 int g_match_tc_dbg = 0;     // timing experiments (v1 kernel): 1 no TMEM reads, 2 TMEM reads only, 3 no MMAs
-int g_match_tc_ver = 2;     // 1 = queries in shared memory (SS), 2 = queries in TMEM (TS)
+int g_match_tc_ver = 4;     // 1 / 2 = E4M3 operands, queries in smem / TMEM; 3 / 4 = E2M1 operands (kind::mxf4), queries in smem / TMEM
 
 static constexpr int TC_TILE = 128;                      // rows per operand tile (UMMA M and N)
 static constexpr int TC_KB = 4;                          // K-blocks of 128 B per row (512 E4M3)
@@ -206,6 +206,31 @@ __device__ __forceinline__ void tc_epilogue_tile(uint32_t t, uint32_t row0, int 
         for (int i = 0; i < 32; ++i) if (96 + i >= valid) vb[i] = -1e30f;
     }
     tc_process32(vb, row0 + 96, st);
+}
+
+// Same tile, all four loads issued at once: the accumulator buffer goes back to the MMA warp after ONE TMEM round trip
+// and the scan of the 128 distances overlaps the next MMA pass (used where the tensor pipe outruns a serial epilogue).
+template <bool MASKED>
+__device__ __forceinline__ void tc_epilogue_tile_wide(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcState& st) {
+    float v0[32], v1[32], v2[32], v3[32];
+    tc_ld32(t, v0); tc_ld32(t + 32, v1); tc_ld32(t + 64, v2); tc_ld32(t + 96, v3);
+    tc_wait_ld();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) tc_mbar_arrive(bar_release);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if (i >= valid) v0[i] = -1e30f;
+            if (32 + i >= valid) v1[i] = -1e30f;
+            if (64 + i >= valid) v2[i] = -1e30f;
+            if (96 + i >= valid) v3[i] = -1e30f;
+        }
+    }
+    tc_process32(v0, row0, st);
+    tc_process32(v1, row0 + 32, st);
+    tc_process32(v2, row0 + 64, st);
+    tc_process32(v3, row0 + 96, st);
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -665,10 +690,190 @@ match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restri
                 if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
                 continue;
             }
-            if (j < full_tiles) tc_epilogue_tile<false>(tbase, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * m, lane, st);
-            else                tc_epilogue_tile<true>(tbase, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * m, lane, st);
+            if (j < full_tiles) tc_epilogue_tile_wide<false>(tbase, (uint32_t)(j * TC_TILE), TC_TILE, bar_tempty + 8 * m, lane, st);
+            else                tc_epilogue_tile_wide<true>(tbase, (uint32_t)(j * TC_TILE), chunk_rows - j * TC_TILE, bar_tempty + 8 * m, lane, st);
         }
         if (qi < nQ) partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(st.best, st.second);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+// ---- v4: v3 with the query tiles in TMEM (TS mode) and 16 epilogue warps --------------------------------
+// tools/tc_dbg.py on v3: 5.4 T cmp/s, 6.1 T with the epilogue's TMEM reads disabled -- the scan of 128 distances per
+// thread per tile had become the long pole.  Here every accumulator row is shared by two threads (64 columns each),
+// both loads are issued at once and the buffer is handed back after one TMEM round trip; the two halves of a query are
+// merged by packed key at the end (exact: min of the bests, second smallest of the four).  The queries sit in TMEM
+// (columns 320-447, 8 E2M1 per 32-bit column), so shared memory is a 14-stage DB ring again.
+static constexpr int TC4_EPI_WARPS = 16;
+static constexpr int TC4_THREADS = 32 * (2 + TC4_EPI_WARPS);
+static constexpr int TC4_STAGES = 14;
+static constexpr int TC4_SMEM_B = TC4_STAGES * TC_KB_BYTES;
+static constexpr int TC4_SMEM_TOTAL = TC4_SMEM_B + TC2_SMEM_BAR + 1024;
+
+__device__ __forceinline__ void tc_mma_mxf4_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t accumulate, uint32_t sfa, uint32_t sfb) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], [%1], %2, %3, [%5], [%6], p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(TC3_IDESC), "r"(accumulate), "r"(sfa), "r"(sfb) : "memory");
+}
+
+template <bool MASKED>
+__device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcState& st) {
+    float v0[32], v1[32];
+    tc_ld32(t, v0); tc_ld32(t + 32, v1);
+    tc_wait_ld();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) tc_mbar_arrive(bar_release);
+    if (MASKED) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            if (i >= valid) v0[i] = -1e30f;
+            if (32 + i >= valid) v1[i] = -1e30f;
+        }
+    }
+    tc_process32(v0, row0, st);
+    tc_process32(v1, row0 + 32, st);
+}
+
+__global__ void __launch_bounds__(TC4_THREADS, 1)
+match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                 uint2* __restrict__ partial, int dbg) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t sB = (raw + 1023u) & ~1023u;
+    const uint32_t sBar = sB + TC4_SMEM_B;
+    const uint32_t bar_full = sBar, bar_empty = sBar + 8 * TC4_STAGES, bar_a = sBar + 16 * TC4_STAGES;
+    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 16, tmem_slot = bar_tempty + 16;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
+    uint2* smem_res = reinterpret_cast<uint2*>(tc_smem_raw + (sB - raw));      // ring reused after the sweep
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+
+    if (tid == 0) {
+        for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
+        tc_mbar_init(bar_a, TC4_EPI_WARPS);
+        for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC4_EPI_WARPS / 2); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+    // TMEM map: 0-127 / 128-255 accumulators D_0 / D_1; 256-319 unit scale factors; 320-383 / 384-447 query tiles A_0 / A_1
+    const uint32_t tm_sf = tmem + 256u, tm_a = tmem + 320u;
+
+    if (warp == 0) {
+        const uint8_t* tsrc = Tx + (size_t)tile0 * TC3_TILE_BYTES;
+        const int nit = ntiles * TC3_KB;
+        for (int it = 0; it < nit; ++it) {
+            const int s = it % TC4_STAGES;
+            tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC4_STAGES) & 1) ^ 1));
+            if (tc_elect_one()) {
+                tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
+                tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        tc_mbar_wait(bar_a, 0);
+        tc_fence_after();
+        const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        for (int j = 0; j < ntiles; ++j) {
+#pragma unroll
+            for (int m = 0; m < TC_QTILES; ++m) {
+                tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
+                tc_fence_after();
+#pragma unroll
+                for (int kb = 0; kb < TC3_KB; ++kb) {
+                    const int it = j * TC3_KB + kb;
+                    const int s = it % TC4_STAGES;
+                    if (m == 0) {
+                        tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC4_STAGES) & 1));
+                        tc_fence_after();
+                    }
+                    if (tc_elect_one()) {
+                        const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+                        const uint32_t a0 = tm_a + (uint32_t)(m * 64 + kb * 32);
+                        const uint32_t d0 = tmem + (uint32_t)(m * TC_TILE);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0), tm_sf, tm_sf + 32u);
+                        if (m == TC_QTILES - 1) tc_commit(bar_empty + 8 * s);
+                        if (kb == TC3_KB - 1) tc_commit(bar_tfull + 8 * m);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        const int e = warp - 2;
+        const int quarter = warp & 3, m = (e >> 2) & 1, half = e >> 3;
+        const int row = quarter * 32 + lane;
+        const int qi = blockIdx.x * TC_QROWS + m * TC_TILE + row;
+        const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+        {
+            uint32_t r[32];
+            if (e < 4) {      // unit scale factors, 128 lanes x 64 columns
+#pragma unroll
+                for (int c = 0; c < 32; ++c) r[c] = 0x7F7F7F7Fu;
+                tc_st32(lane_base + 256u, r);
+                tc_st32(lane_base + 288u, r);
+            }
+            // this thread's half of its query: 8 packed words -> 32 TMEM columns of 8 E2M1 each
+            uint4 q4[2];
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+                q4[i] = qi < nQ ? __ldg(reinterpret_cast<const uint4*>(Q + (size_t)qi * 16 + half * 8) + i) : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t w[8] = {q4[0].x, q4[0].y, q4[0].z, q4[0].w, q4[1].x, q4[1].y, q4[1].z, q4[1].w};
+#pragma unroll
+            for (int c = 0; c < 32; ++c) r[c] = qi < nQ ? tc_nib4((w[c >> 2] >> (8 * (c & 3))) & 255u) : 0u;
+            tc_st32(lane_base + 320u + (uint32_t)(m * 64 + half * 32), r);
+            tc_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc_mbar_arrive(bar_a);
+        }
+        const uint32_t tbase = lane_base + (uint32_t)(m * TC_TILE + half * 64);
+        TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
+        for (int j = 0; j < ntiles; ++j) {
+            tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
+            tc_fence_after();
+            if (dbg == 1) {
+                tc_fence_before(); __syncwarp();
+                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                continue;
+            }
+            const int valid = chunk_rows - j * TC_TILE - half * 64;       // rows of this half that exist
+            const uint32_t row0 = (uint32_t)(j * TC_TILE + half * 64);
+            if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + 8 * m, lane, st);
+            else             tc_epilogue_half_tile<true>(tbase, row0, valid, bar_tempty + 8 * m, lane, st);
+        }
+        // merge the two column halves of each query by packed key.  The staging array aliases ring stage 0, which the
+        // last tile's MMAs of the OTHER query tile may still be reading: wait until every epilogue warp has seen its last tile.
+        asm volatile("bar.sync 1, %0;" ::"n"(TC4_EPI_WARPS * 32) : "memory");
+        if (half == 1) smem_res[m * TC_TILE + row] = make_uint2(st.best, st.second);
+        asm volatile("bar.sync 1, %0;" ::"n"(TC4_EPI_WARPS * 32) : "memory");
+        if (half == 0 && qi < nQ) {
+            const uint2 o = smem_res[m * TC_TILE + row];
+            const uint32_t b = min(st.best, o.x);
+            const uint32_t sec = min(max(st.best, o.x), min(st.second, o.y));
+            partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(b, sec);
+        }
     }
 
     tc_fence_before();
@@ -687,8 +892,8 @@ bool tc_wanted(int nQ, int nT) {
 }
 
 int tc_version() { return g_match_tc_ver; }
-size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (g_match_tc_ver == 3 ? TC3_SMEM_A : TC_SMEM_A); }
-size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (g_match_tc_ver == 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
+size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (g_match_tc_ver >= 3 ? TC3_SMEM_A : TC_SMEM_A); }
+size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (g_match_tc_ver >= 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
 
 int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s) {
     if (out_bytes == 0) return CLB_OK;
@@ -696,7 +901,7 @@ int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, 
     const size_t blocks = (chunks + 255) / 256;
     if (blocks > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "descriptor set too large to expand"); return CLB_EINVAL; }
     timer("expand").begin(s);
-    if (g_match_tc_ver == 3)
+    if (g_match_tc_ver >= 3)
         expand4_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
     else
         expand_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
@@ -748,11 +953,15 @@ int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const voi
         CLB_CUDA(cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
         CLB_CUDA(cudaFuncSetAttribute(match_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_TOTAL));
         CLB_CUDA(cudaFuncSetAttribute(match_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC3_SMEM_TOTAL));
+        CLB_CUDA(cudaFuncSetAttribute(match_tc4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC4_SMEM_TOTAL));
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     dim3 grid(qblocks, nchunks);
     timer("match").begin(s);
-    if (g_match_tc_ver == 3 && Qx)
+    if (g_match_tc_ver == 4)
+        match_tc4_kernel<<<grid, TC4_THREADS, TC4_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
+                                                                 reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
+    else if (g_match_tc_ver == 3 && Qx)
         match_tc3_kernel<<<grid, TC_THREADS, TC3_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
                                                                 reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
     else if (g_match_tc_ver == 1 && Qx)

@@ -151,10 +151,10 @@ def tc_forced(clb):
     """force the tcgen05 kernels at every size (the default picks them from 2^24 comparisons up)"""
     clb.set_param("match_tc", 1)
     yield
-    clb.set_param("match_tc", -1); clb.set_param("match_tc_ver", 2); clb.set_param("match_tc_chunks", 0)
+    clb.set_param("match_tc", -1); clb.set_param("match_tc_ver", 4); clb.set_param("match_tc_chunks", 0)
 
 
-@pytest.mark.parametrize("ver", [2, 1])
+@pytest.mark.parametrize("ver", [4, 3, 2, 1])
 @pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (3, 1), (7, 5), (33, 64), (64, 65), (128, 128), (255, 257), (256, 129),
                                    (300, 1000), (1000, 777), (2049, 4100), (5000, 5000)])
 def test_match_tc_vs_oracle(clb, oracle, matcher, tc_forced, nq, nt, ver):
@@ -169,6 +169,20 @@ def test_match_tc_vs_oracle(clb, oracle, matcher, tc_forced, nq, nt, ver):
     for thr in (40, 60, 0):
         _check_match(clb, oracle, matcher, Q, T, thr)
     assert clb.get_param("last_match_path") == ver
+
+
+def test_match_tc_ragged_tail_race(clb, oracle, matcher, tc_forced):
+    """20 000 x 20 000: 157 DB tiles (ragged last tile) over several chunks; the shape that exposed the v4 staging race"""
+    T = synth.random_descriptors(20000, 31); Q, _ = synth.planted_queries(T, 20000, 32)
+    for _ in range(3):
+        got = matcher.compute_matches(Q, T, 40, want_dist=True)
+        clb.set_param("match_tc", 0)
+        ref = matcher.compute_matches(Q, T, 40, want_dist=True)
+        clb.set_param("match_tc", 1)
+        assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+    sl = slice(16000, 16064)
+    ro = oracle.match_2nn(Q[sl], T, 40)
+    assert all(np.array_equal(a[sl], b) for a, b in zip(got, ro))
 
 
 @pytest.mark.parametrize("chunks", [1, 2, 5])
@@ -209,7 +223,7 @@ def test_match_tc_golden_map_and_shards(clb, oracle, matcher, tc_forced):
 def test_match_default_path_is_tensor_core_at_size(clb, matcher):
     T = synth.random_descriptors(5000, 1); Q = synth.random_descriptors(5000, 2)
     matcher.compute_matches(Q, T, 40)
-    assert clb.get_param("last_match_path") == 2              # 2.5e7 comparisons >= 2^24
+    assert clb.get_param("last_match_path") == 4              # 2.5e7 comparisons >= 2^24
     matcher.compute_matches(Q[:100], T[:100], 40)
     assert clb.get_param("last_match_path") == 0
 
