@@ -147,19 +147,23 @@ expand_kernel(const uint32_t* __restrict__ rows, int n, size_t n_chunks16, uint4
 // per-thread epilogue state
 struct TcState { uint32_t best, second; float thr; };
 
-// 32 accumulator columns (DB rows row0 .. row0+31 of the chunk) for this thread's query
+// 32 accumulator columns (DB rows row0 .. row0+31 of the chunk) for this thread's query, in two groups of 16:
+// a group costs 8 three-input max ops + 1 compare + 1 branch unless one of its distances beats the current second best
+__device__ __forceinline__ float tc_max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0, TcState& st) {
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        const float m = fmaxf(fmaxf(fmaxf(v[8 * g + 0], v[8 * g + 1]), fmaxf(v[8 * g + 2], v[8 * g + 3])),
-                              fmaxf(fmaxf(v[8 * g + 4], v[8 * g + 5]), fmaxf(v[8 * g + 6], v[8 * g + 7])));
+    for (int g = 0; g < 2; ++g) {
+        const float* x = &v[16 * g];
+        const float m0 = tc_max3(x[0], x[1], x[2]), m1 = tc_max3(x[3], x[4], x[5]), m2 = tc_max3(x[6], x[7], x[8]);
+        const float m3 = tc_max3(x[9], x[10], x[11]), m4 = tc_max3(x[12], x[13], x[14]);
+        const float m = tc_max3(tc_max3(m0, m1, m2), tc_max3(m3, m4, x[15]), -1e30f);
         if (m > st.thr) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float x = v[8 * g + e];
-                if (x > st.thr) {   // thr only rises, so testing against the group-entry value is exact
-                    const uint32_t d = (uint32_t)(512 - __float2int_rn(x)) >> 1;
-                    const uint32_t key = (d << TC_KEY_SHIFT) | (row0 + 8 * g + e);
+            for (int e = 0; e < 16; ++e) {
+                const float xe = x[e];
+                if (xe > st.thr) {   // thr only rises, so testing against the group-entry value is exact
+                    const uint32_t d = (uint32_t)(512 - __float2int_rn(xe)) >> 1;
+                    const uint32_t key = (d << TC_KEY_SHIFT) | (row0 + 16 * g + e);
                     const uint32_t mx = max(key, st.best);
                     st.second = min(st.second, mx);
                     st.best = min(st.best, key);
