@@ -222,7 +222,7 @@ __device__ __forceinline__ float feature_angle(const uint8_t* __restrict__ img, 
     return fast_atan2_ref((float)ys, (float)xs);
 }
 
-// one warp per global row: ordered compaction + angle
+// one warp per global row: ordered compaction, 128 map bytes per step (one 32-bit load per lane, 4 ballots)
 __global__ void __launch_bounds__(256)
 compact_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__ nms_map,
                const int* __restrict__ row_count, const int* __restrict__ row_off,
@@ -235,23 +235,46 @@ compact_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__
     while (L + 1 < rm.n && grow >= rm.row_base[L + 1]) ++L;
     const int y = grow - rm.row_base[L];
     const int w = lt.w[L];
-    const uint8_t* row = nms_map + (size_t)grow * lt.stride[0];
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(nms_map + (size_t)grow * lt.stride[0]);   // stride0 is 128-B aligned
     int out = row_off[grow];
-    for (int xb = 0; xb < w; xb += 32) {
-        const int x = xb + lane;
-        const int s = x < w ? row[x] : 0;
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, s != 0);
-        if (s) {
-            const int pos = out + __popc(bal & ((1u << lane) - 1));
-            if (pos < cap) {
-                clb_keypoint k;
-                k.x = x; k.y = y; k.score = (uint8_t)s; k._pad0[0] = k._pad0[1] = k._pad0[2] = 0;
-                k.angle = feature_angle(lt.img[L], x, y, lt.stride[L]);
-                k.scale = (uint8_t)L; k._pad1[0] = k._pad1[1] = k._pad1[2] = 0;
-                kps[pos] = k;
+    for (int xb = 0; xb < w; xb += 128) {
+        const int x0 = xb + lane * 4;
+        uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;      // bytes beyond w inside the padded stride are never written: mask them
+        if (x0 + 3 >= w) {
+            const int keep = w - x0;                             // 1..3 valid bytes (or <= 0)
+            v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - keep)))) : 0u;
+        }
+        // order inside the 128-px step is x = xb + 4*lane + k: count lanes below (all 4 bytes) + own lower bytes
+        const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
+        uint32_t pre = nz;                                       // inclusive warp scan of nz
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+        int pos = out + (int)(pre - nz);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t s = (v >> (8 * k)) & 0xFFu;
+            if (s) {
+                if (pos < cap) {
+                    clb_keypoint kp;
+                    kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)s; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
+                    kp.angle = 0.f;
+                    kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
+                    kps[pos] = kp;
+                }
+                ++pos;
             }
         }
-        out += __popc(bal);
+        out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+    }
+}
+
+// orientation, one thread per keypoint (FeatureAngle.h:197-247)
+__global__ void __launch_bounds__(256)
+angle_kernel(const LevelTable lt, clb_keypoint* __restrict__ kps, const int* __restrict__ d_total, int cap) {
+    const int n = min(*d_total, cap);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int L = kps[i].scale;
+        kps[i].angle = feature_angle(lt.img[L], kps[i].x, kps[i].y, lt.stride[L]);
     }
 }
 
@@ -288,6 +311,8 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);
     CLB_LAUNCHED();
     compact_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, row_off, d_kps, cap);
+    CLB_LAUNCHED();
+    angle_kernel<<<296, 256, 0, s>>>(lt, d_kps, d_total, cap);
     timer("fast").end(s);
     CLB_LAUNCHED();
     return CLB_OK;
