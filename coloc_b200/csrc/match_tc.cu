@@ -158,15 +158,23 @@ __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0
         const float m3 = tc_max3(x[9], x[10], x[11]), m4 = tc_max3(x[12], x[13], x[14]);
         const float m = tc_max3(tc_max3(m0, m1, m2), tc_max3(m3, m4, x[15]), -1e30f);
         if (m > st.thr) {
+            // rare after the first tiles, and then usually one element of one lane: descend by sub-groups of 4 so the
+            // warp does not replay 16 predicated updates for it
 #pragma unroll
-            for (int e = 0; e < 16; ++e) {
-                const float xe = x[e];
-                if (xe > st.thr) {   // thr only rises, so testing against the group-entry value is exact
-                    const uint32_t d = (uint32_t)(512 - __float2int_rn(xe)) >> 1;
-                    const uint32_t key = (d << TC_KEY_SHIFT) | (row0 + 16 * g + e);
-                    const uint32_t mx = max(key, st.best);
-                    st.second = min(st.second, mx);
-                    st.best = min(st.best, key);
+            for (int q = 0; q < 4; ++q) {
+                const float m4 = fmaxf(tc_max3(x[4 * q], x[4 * q + 1], x[4 * q + 2]), x[4 * q + 3]);
+                if (m4 > st.thr) {
+#pragma unroll
+                    for (int e = 4 * q; e < 4 * q + 4; ++e) {
+                        const float xe = x[e];
+                        if (xe > st.thr) {   // thr only rises, so testing against the group-entry value is exact
+                            const uint32_t d = (uint32_t)(512 - __float2int_rn(xe)) >> 1;
+                            const uint32_t key = (d << TC_KEY_SHIFT) | (row0 + 16 * g + e);
+                            const uint32_t mx = max(key, st.best);
+                            st.second = min(st.second, mx);
+                            st.best = min(st.best, key);
+                        }
+                    }
                 }
             }
             st.thr = st.second == 0xFFFFFFFFu ? -1e30f : (float)(512 - 2 * (int)(st.second >> TC_KEY_SHIFT));
@@ -928,16 +936,16 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
         best_c = g_match_tc_chunks < max_chunks ? g_match_tc_chunks : max_chunks;
         if (best_c < min_chunks) best_c = min_chunks;
     } else {
-        double best_eff = -1.0;
+        // time model (tools/tc_small.py): a CTA costs ~0.8 us per DB tile plus ~15 us of prologue and epilogue warm-up
+        // (every query's threshold starts open), and the busiest SM runs `waves` CTAs back to back
+        double best_t = 1e30;
         for (int c = best_c; c <= max_chunks; ++c) {
             const int tpc = (total_tiles + c - 1) / c;
             const int real_c = (total_tiles + tpc - 1) / tpc;
             const long long ctas = (long long)qblocks * real_c;
             const long long waves = (ctas + sm_count - 1) / sm_count;
-            // work done / work slots: the busiest SM runs `waves` CTAs of tpc tiles
-            const double eff = (double)qblocks * total_tiles / ((double)waves * sm_count * tpc);
-            if (eff > best_eff + 0.02) { best_eff = eff; best_c = c; }
-            if (best_eff >= 0.95) break;
+            const double t = (double)waves * (0.8 * tpc + 15.0);
+            if (t < best_t * 0.98) { best_t = t; best_c = c; }
         }
     }
     const int tpc = (total_tiles + best_c - 1) / best_c;
