@@ -268,6 +268,17 @@ class Matcher:
         _check(lib().clb_match_partial_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), C.c_int64(int(t_base)),
                                            _dptr(d_partial), _sarg(stream)))
 
+    def set_map_dev(self, dM, nM, stream=None):
+        """device-resident map / DB shard (copied D2D once, expanded once for the tensor-core path)"""
+        _check(lib().clb_set_map_dev(self._h, _dptr(dM), int(nM), _sarg(stream)))
+
+    def match_map_dev(self, dQ, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
+        _check(lib().clb_match_map_dev(self._h, _dptr(dQ), int(nQ), int(threshold), _dptr(d_match), _dptr(d_best), _dptr(d_second),
+                                       _sarg(stream)))
+
+    def match_map_partial_dev(self, dQ, nQ, t_base, d_partial, stream=None):
+        _check(lib().clb_match_map_partial_dev(self._h, _dptr(dQ), int(nQ), C.c_int64(int(t_base)), _dptr(d_partial), _sarg(stream)))
+
     def merge_partials_dev(self, d_parts, nparts, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
         _check(lib().clb_merge_partials_dev(self._h, _dptr(d_parts), int(nparts), int(nQ), int(threshold),
                                             _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))

@@ -173,6 +173,47 @@ int clb_match_map(clb_matcher* m, const uint64_t* Q, int nQ, int threshold,
                     match_out, best_d_out, second_d_out, true);
 }
 
+int clb_set_map_dev(clb_matcher* m, const uint64_t* dM, int nM, void* stream) {
+    if (!m || nM < 0 || (nM > 0 && !dM)) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(m->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    CLB_CUDA(m->map.reserve((size_t)(nM > 0 ? nM : 1) * 64));
+    if (nM > 0) CLB_CUDA(cudaMemcpyAsync(m->map.p, dM, (size_t)nM * 64, cudaMemcpyDeviceToDevice, s));
+    m->n_map = nM;
+    m->mapx_valid = false;
+    return CLB_OK;
+}
+
+int clb_match_map_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int threshold,
+                      int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream) {
+    if (!m || nQ < 0 || (nQ > 0 && !dQ)) return CLB_EINVAL;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    int rc = ensure(m, nQ, m->n_map);
+    if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    const void *Qx, *Tx;
+    rc = prepare_tc(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, true, s, &Qx, &Tx);
+    if (rc) return rc;
+    return launch_match(dQ, nQ, m->map.as<uint64_t>(), m->n_map, 0, m->scratch.p, m->scratch.cap, m->sm_count,
+                        threshold < 0 ? m->o.thresh : threshold, 0.f, d_match_out, d_best_out, d_second_out, nullptr, s, Qx, Tx);
+}
+
+int clb_match_map_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int64_t t_base,
+                              clb_partial* d_partial_out, void* stream) {
+    if (!m || nQ < 0 || (nQ > 0 && (!dQ || !d_partial_out))) return CLB_EINVAL;
+    if (nQ == 0) return CLB_OK;
+    CLB_CUDA(cudaSetDevice(m->device));
+    int rc = ensure(m, nQ, m->n_map);
+    if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    const void *Qx, *Tx;
+    rc = prepare_tc(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, true, s, &Qx, &Tx);
+    if (rc) return rc;
+    return launch_match(dQ, nQ, m->map.as<uint64_t>(), m->n_map, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
+                        nullptr, nullptr, nullptr, d_partial_out, s, Qx, Tx);
+}
+
 int clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT,
                           int64_t t_base, clb_partial* d_partial_out, void* stream) {
     int rc = check_sets(m, dQ, nQ, dT, nT);

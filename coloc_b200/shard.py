@@ -64,6 +64,8 @@ class ShardedMatcher:
     def set_shard_dev(self, dT_rows, t_base):
         """dT_rows: int64 CUDA tensor [n_local, 8] (device-resident shard), t_base: global index of row 0."""
         self.dT, self.n_local, self.t_base = dT_rows, int(dT_rows.shape[0]), int(t_base)
+        # resident shard: copied and expanded once inside the matcher (GPUMatcher::setMapData analogue), not per step
+        self.m.set_map_dev(dT_rows, self.n_local, stream=self.torch.cuda.current_stream().cuda_stream)
 
     def set_shard(self, T_rows_host, t_base):
         t = self.torch.from_numpy(np.ascontiguousarray(T_rows_host, np.uint64).view(np.int64).reshape(-1, 8))
@@ -75,11 +77,11 @@ class ShardedMatcher:
         torch, dist = self.torch, self.dist
         stream = torch.cuda.current_stream().cuda_stream   # 0 (legacy default) is mapped to cudaStreamLegacy by the binding
         if self.world == 1:
-            self.m.match_dev(dQ, nQ, self.dT, self.n_local, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
+            self.m.match_map_dev(dQ, nQ, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
             return
         local = parts_buf if parts_buf is not None else torch.empty((nQ, 4), dtype=torch.int32, device=dQ.device)
         allp = gather_buf if gather_buf is not None else torch.empty((self.world, nQ, 4), dtype=torch.int32, device=dQ.device)
-        self.m.match_partial_dev(dQ, nQ, self.dT, self.n_local, self.t_base, local, stream=stream)
+        self.m.match_map_partial_dev(dQ, nQ, self.t_base, local, stream=stream)
         dist.all_gather_into_tensor(allp.view(-1), local.view(-1), group=self.group)   # the one exchange step
         self.m.merge_partials_dev(allp, self.world, nQ, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
 

@@ -149,6 +149,15 @@ int  clb_set_map(clb_matcher* m, const uint64_t* M, int nM);
 int  clb_match_map(clb_matcher* m, const uint64_t* Q, int nQ, int threshold,
                    int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
 
+/* device-resident variants: the map / DB shard is copied device-to-device once (and expanded once for
+ * the tensor-core path), every later call only brings queries.  dM / dQ are DEVICE pointers, 16-byte aligned; enqueue only.
+ * clb_match_map_partial_dev is the DB-row-sharding step on the resident rows (global indices start at t_base). */
+int  clb_set_map_dev(clb_matcher* m, const uint64_t* dM, int nM, void* stream);
+int  clb_match_map_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int threshold,
+                       int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+int  clb_match_map_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int64_t t_base,
+                               clb_partial* d_partial_out, void* stream);
+
 /* ratio-test mode mirroring the CPU build (CPUMatcher.hpp:67-76 -> matching_filters.hpp:39-60):
  * keep iff best < ratio * second (float compare).  HOST pointers. */
 int  clb_match_2nn_ratio(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T, int nT, float ratio,

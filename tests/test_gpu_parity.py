@@ -386,3 +386,45 @@ def test_frame_stream_equals_single_frame_calls(clb, depth):
     with pytest.raises(clb.ClbError):
         fs.next()
     fs.close()
+
+
+@pytest.mark.parametrize("tc", [0, 1])
+def test_resident_map_dev_api(clb, oracle, tc):
+    """clb_set_map_dev / clb_match_map_dev / clb_match_map_partial_dev: the resident shard is copied (and expanded) once,
+    several query sets follow; a new map replaces the cached expansion; partials of two resident shards merge exactly."""
+    import torch
+    clb.set_param("match_tc", tc)
+    try:
+        nq = 900
+        outs = []
+        m = clb.Matcher(maxkp=4096)
+        for seed, nt in ((5, 3000), (6, 2177)):
+            T = synth.random_descriptors(nt, seed); T[nt - 1] = T[3]
+            dT = torch.from_numpy(T.view(np.int64)).cuda()
+            m.set_map_dev(dT, nt)
+            dT.zero_()                                        # the matcher owns a copy
+            for qs in (7, 8):
+                Q, _ = synth.planted_queries(T, nq, qs); Q[0] = T[3]
+                dQ = torch.from_numpy(Q.view(np.int64)).cuda()
+                out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+                m.match_map_dev(dQ, nq, 60, out[0], out[1], out[2])
+                torch.cuda.synchronize()
+                ref = oracle.match_2nn(Q, T, 60)
+                assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
+        # two resident shards (two matchers), partial + merge == single scan
+        T = synth.random_descriptors(5000, 9); Q, _ = synth.planted_queries(T, nq, 10)
+        dQ = torch.from_numpy(Q.view(np.int64)).cuda()
+        parts = torch.zeros((2, nq, 4), dtype=torch.int32, device="cuda")
+        m2 = clb.Matcher(maxkp=4096)
+        for i, (mm, a, b) in enumerate(((m, 0, 2600), (m2, 2600, 5000))):
+            mm.set_map_dev(torch.from_numpy(T[a:b].view(np.int64)).cuda(), b - a)
+            mm.match_map_partial_dev(dQ, nq, a, parts[i])
+        torch.cuda.synchronize()
+        out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+        m.merge_partials_dev(parts, 2, nq, 40, out[0], out[1], out[2])
+        torch.cuda.synchronize()
+        ref = oracle.match_2nn(Q, T, 40)
+        assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
+        m.close(); m2.close()
+    finally:
+        clb.set_param("match_tc", -1)
