@@ -316,6 +316,10 @@ def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
         allm = torch.empty((world, slice_max), dtype=torch.int32, device=dev)
         m = clb.Matcher(maxkp=max(counts) + 16, device=dev.index)
         st = torch.cuda.current_stream().cuda_stream
+        fm = clb.FeatureMap(device=dev.index)                # device-resident FeatureMap: each view's rows uploaded / expanded once
+        for k in range(4):
+            fm.put_dev(k, descs[k], counts[k], stream=st)
+        jobs = m._pairs([(pairs[p][0], pairs[p][1], a, b) for p, a, b in plan])
     except Exception as e:
         ok = 0; err = repr(e)
     flag = torch.tensor([ok], dtype=torch.int32, device=dev)
@@ -324,38 +328,51 @@ def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
     if int(flag.item()) == 0:
         return {"error": err if not ok else "another rank failed"}
 
-    def step():
+    def step_calls():                                         # one clb_match_2nn_dev call per pair (expand + sweep + merge each)
         off = 0
         for p, a, b in plan:
             qi, ti = pairs[p]
             m.match_dev(descs[qi][a:b], b - a, descs[ti], counts[ti], 40, mine[off:off + (b - a)], stream=st)
             off += b - a
-        if world > 1:
-            dist.all_gather_into_tensor(allm.view(-1), mine)
-        else:
-            allm[0].copy_(mine)
 
-    for _ in range(3):
-        step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record(); torch.cuda.synchronize()
-    tm = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    ms = float(tm.item()) / steps
+    def step_list():                                          # the whole pair list: one sweep launch + one merge launch
+        m.match_pairs_dev(fm, jobs, 40, mine, stream=st)
+
+    def timed(fn):
+        def step():
+            fn()
+            if world > 1:
+                dist.all_gather_into_tensor(allm.view(-1), mine)
+            else:
+                allm[0].copy_(mine)
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record(); torch.cuda.synchronize()
+        tm = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        return float(tm.item()) / steps
+
+    ms_calls = timed(step_calls)
+    ref_rows = allm.clone()
+    ms = timed(step_list)
+    same = bool(torch.equal(ref_rows, allm))
     cmp_step = float(sum(counts[q] * counts[t] for q, t in pairs))
     got = allm.cpu().numpy()
     matched = int(sum((got[r][:shard.shard_range(total_rows, r, world)[1] - shard.shard_range(total_rows, r, world)[0]] >= 0).sum()
                       for r in range(world)))
-    m.close()
+    m.close(); fm.close()
     return {"frames": 4, "pairs": 12, "keypoints": counts, "query_rows": total_rows, "comparisons_per_step": cmp_step,
             "ms_per_step": ms, "comparisons_per_s": cmp_step / (ms * 1e-3), "matched_rows": matched,
+            "api": "clb_match_pairs_dev over a device FeatureMap (one sweep + one merge launch per step)",
+            "per_pair_calls": {"ms_per_step": ms_calls, "comparisons_per_s": cmp_step / (ms_calls * 1e-3), "same_matches": same},
             "parallelism": f"query rows x{world}, all-gather of int32 match lists"}
 
 

@@ -12,7 +12,10 @@ KP_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "u1"), ("_p0", "u1", 
 PARTIAL_DTYPE = np.dtype([("best_d", "<i4"), ("best_i", "<i4"), ("second_d", "<i4"), ("_pad", "<i4")])
 assert KP_DTYPE.itemsize == 20 and PARTIAL_DTYPE.itemsize == 16
 
-OK, EINVAL, ECUDA, ECAPACITY, ENOMEM, EUNSUPPORTED = range(6)
+OK, EINVAL, ECUDA, ECAPACITY, ENOMEM, EUNSUPPORTED, ENOTFOUND = range(7)
+PAIR_DTYPE = np.dtype([("query_idx", "<u4"), ("train_idx", "<u4"), ("q_lo", "<i4"), ("q_hi", "<i4")])
+OBS_DTYPE = np.dtype([("idx", "<u4"), ("feat", "<u4")])
+UNDEFINED_FEAT = 0xFFFFFFFF
 
 
 class ClbError(RuntimeError):
@@ -282,6 +285,110 @@ class Matcher:
     def merge_partials_dev(self, d_parts, nparts, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
         _check(lib().clb_merge_partials_dev(self._h, _dptr(d_parts), int(nparts), int(nQ), int(threshold),
                                             _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))
+
+
+    # ---- device FeatureMap: pair lists and the map database (SURVEY 8f) ---------------------
+    @staticmethod
+    def _pairs(pairs):
+        """[(query_idx, train_idx)] or [(query_idx, train_idx, q_lo, q_hi)] -> clb_pair array"""
+        a = np.zeros(len(pairs), PAIR_DTYPE)
+        for k, p in enumerate(pairs):
+            a[k] = (p[0], p[1], p[2] if len(p) > 2 else 0, p[3] if len(p) > 3 else -1)
+        return a
+
+    def pair_rows(self, fmap, pairs):
+        a = self._pairs(pairs)
+        n = C.c_longlong(0)
+        _check(lib().clb_match_pairs_rows(self._h, fmap._h, _ptr(a), len(a), C.byref(n)))
+        return int(n.value)
+
+    def match_pairs(self, fmap, pairs, threshold=40, ratio=0.0, want_dist=False):
+        """GPUMatcher::computeMatches(FeatureMap&, PairWiseMatches&) (GPUMatcher.hpp:143-155) over device-resident sets, the
+        whole list in one launch.  Returns one match[] array per pair (and best / second when want_dist)."""
+        a = self._pairs(pairs)
+        tot = self.pair_rows(fmap, pairs)
+        m, b, s = self._outs(tot, want_dist)
+        _check(lib().clb_match_pairs(self._h, fmap._h, _ptr(a), len(a), int(threshold), C.c_float(ratio), _ptr(m), _ptr(b), _ptr(s)))
+        cuts, off = [], 0
+        for p in a:
+            n = (fmap.count(int(p["query_idx"])) if p["q_hi"] < 0 else int(p["q_hi"])) - int(p["q_lo"])
+            cuts.append((off, off + n)); off += n
+        split = lambda v: [v[x:y] for x, y in cuts]
+        return (split(m), split(b), split(s)) if want_dist else split(m)
+
+    def match_pairs_dev(self, fmap, pairs, threshold, d_match, d_best=None, d_second=None, ratio=0.0, stream=None):
+        a = pairs if isinstance(pairs, np.ndarray) and pairs.dtype == PAIR_DTYPE else self._pairs(pairs)
+        _check(lib().clb_match_pairs_dev(self._h, fmap._h, _ptr(a), len(a), int(threshold), C.c_float(ratio),
+                                         _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))
+
+    def set_map_from_fmap(self, fmap, obs, stream=None):
+        """colocData::setupMapDatabase (colocData.hpp:89-121) + setMapData as a device gather: obs = [(set idx, feature id)],
+        entries with feature id UNDEFINED_FEAT are skipped.  Returns the number of map rows."""
+        a = np.ascontiguousarray(np.asarray(obs, dtype=np.int64).reshape(-1, 2).astype(np.uint32)).view(OBS_DTYPE).reshape(-1)
+        n = C.c_int(0)
+        _check(lib().clb_set_map_from_fmap(self._h, fmap._h, _ptr(a), len(a), C.byref(n), _sarg(stream)))
+        return int(n.value)
+
+
+class FeatureMap:
+    """device-side coloc::FeatureMap (idx -> Regions; GPUDetector.hpp:167-182): every frame's descriptors (and keypoints)
+    stay on the GPU between detect and match (clb_fmap_*)."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        _check(lib().clb_fmap_create(int(device), C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            lib().clb_fmap_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __len__(self):
+        return int(lib().clb_fmap_size(self._h))
+
+    def put(self, idx, desc, kps=None):
+        d = np.ascontiguousarray(desc, np.uint64).reshape(-1, 8)
+        k = None
+        if kps is not None:
+            k = np.ascontiguousarray(kps, KP_DTYPE)
+            if len(k) != len(d):
+                raise ValueError("keypoints and descriptors differ in length")
+        _check(lib().clb_fmap_put(self._h, C.c_uint32(idx), _ptr(k), _ptr(d), len(d)))
+
+    def put_dev(self, idx, d_desc, n, d_kps=None, stream=None):
+        _check(lib().clb_fmap_put_dev(self._h, C.c_uint32(idx), _dptr(d_kps), _dptr(d_desc), int(n), _sarg(stream)))
+
+    def count(self, idx):
+        n = C.c_int(0)
+        _check(lib().clb_fmap_count(self._h, C.c_uint32(idx), C.byref(n)))
+        return int(n.value)
+
+    def __contains__(self, idx):
+        n = C.c_int(0)
+        return lib().clb_fmap_count(self._h, C.c_uint32(idx), C.byref(n)) == 0
+
+    def erase(self, idx):
+        _check(lib().clb_fmap_erase(self._h, C.c_uint32(idx)))
+
+    def get(self, idx, want_kps=False):
+        n = self.count(idx)
+        d = np.zeros((n, 8), np.uint64)
+        k = np.zeros(n, KP_DTYPE) if want_kps else None
+        got = C.c_int(0)
+        _check(lib().clb_fmap_get(self._h, C.c_uint32(idx), _ptr(k), _ptr(d), n, C.byref(got)))
+        return (k, d) if want_kps else d
+
+    def desc_dev(self, idx):
+        """(device pointer of the packed rows, device pointer of the keypoints or 0, rows)"""
+        pd, pk, n = C.c_void_p(0), C.c_void_p(0), C.c_int(0)
+        _check(lib().clb_fmap_desc_dev(self._h, C.c_uint32(idx), C.byref(pd), C.byref(pk), C.byref(n)))
+        return int(pd.value or 0), int(pk.value or 0), int(n.value)
 
 
 class FrameStream:

@@ -97,6 +97,7 @@ const char* clb_strerror(int code) {
         case CLB_ECAPACITY: return "output capacity too small";
         case CLB_ENOMEM: return "out of device memory";
         case CLB_EUNSUPPORTED: return "unsupported";
+        case CLB_ENOTFOUND: return "feature set not found";
         default: return "unknown error";
     }
 }

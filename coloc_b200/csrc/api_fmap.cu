@@ -1,0 +1,367 @@
+// api_fmap.cu -- device-resident FeatureMap, batched pair matching and the map-database builder (C ABI, include/coloc_b200.h).
+//
+// The reference keeps every frame's descriptors in host `Regions` (coloc::FeatureMap, idx -> unique_ptr<AKAZE_Binary_Regions>,
+// GPUDetector.hpp:167-182) and re-uploads both sets for every pair (GPUMatcher.hpp:165-172 -> :180-226) and the gathered landmark
+// rows for every map update (colocData.hpp:89-121 -> GPUMatcher.hpp:110-117).  Here a clb_fmap holds each set once on the device,
+// packed rows plus the tensor-core operand image, and
+//   * clb_match_pairs[_dev]   runs a whole pair list (GPUMatcher::computeMatches(FeatureMap&, PairWiseMatches&), :143-155)
+//                             as ONE sweep launch + ONE merge launch,
+//   * clb_set_map_from_fmap   is setupMapDatabase + setMapData as a device gather.
+#include "matcher_priv.cuh"
+#include <map>
+#include <vector>
+#include <algorithm>
+#include <new>
+#include <string.h>
+
+using namespace clb;
+
+namespace {
+
+struct FSet {
+    DevBuf desc, kps, tx;
+    int n = 0;
+    bool has_kps = false;
+    ~FSet() { desc.release(); kps.release(); tx.release(); }
+};
+
+}  // namespace
+
+struct clb_fmap {
+    int device;
+    cudaStream_t stream;
+    std::map<uint32_t, FSet*> sets;
+    DevBuf gather_tab;           // clb_set_map_from_fmap: (slot, feat) list + slot base pointers
+    void* stage;                 // pinned staging for that table
+    size_t stage_cap;
+};
+
+static FSet* find_set(const clb_fmap* f, uint32_t idx) {
+    auto it = f->sets.find(idx);
+    return it == f->sets.end() ? nullptr : it->second;
+}
+
+static int pinned_reserve(void** p, size_t* cap, size_t bytes) {
+    if (bytes <= *cap) return CLB_OK;
+    if (*p) cudaFreeHost(*p);
+    *p = nullptr; *cap = 0;
+    const size_t want = bytes + bytes / 2 + 4096;
+    CLB_CUDA(cudaMallocHost(p, want));
+    *cap = want;
+    return CLB_OK;
+}
+
+// (re)place a set: rows come from host or device memory; the operand image is built right away
+static int put_set(clb_fmap* f, uint32_t idx, const clb_keypoint* kps, const uint64_t* desc, int n, cudaMemcpyKind kind, cudaStream_t s) {
+    if (!f || n < 0 || (n > 0 && !desc)) { snprintf(g_err, sizeof(g_err), "bad feature set"); return CLB_EINVAL; }
+    CLB_CUDA(cudaSetDevice(f->device));
+    FSet* set = find_set(f, idx);
+    if (!set) {
+        set = new (std::nothrow) FSet();
+        if (!set) return CLB_ENOMEM;
+        f->sets[idx] = set;
+    }
+    set->n = 0; set->has_kps = false;
+    CLB_CUDA(set->desc.reserve((size_t)(n > 0 ? n : 1) * 64));
+    CLB_CUDA(set->tx.reserve(tc4_t_bytes(n) + 16));
+    if (n > 0) {
+        CLB_CUDA(cudaMemcpyAsync(set->desc.p, desc, (size_t)n * 64, kind, s));
+        int rc = launch_expand4(set->desc.as<uint64_t>(), n, set->tx.p, s);
+        if (rc) return rc;
+        if (kps) {
+            CLB_CUDA(set->kps.reserve((size_t)n * sizeof(clb_keypoint)));
+            CLB_CUDA(cudaMemcpyAsync(set->kps.p, kps, (size_t)n * sizeof(clb_keypoint), kind, s));
+            set->has_kps = true;
+        }
+    }
+    set->n = n;
+    return CLB_OK;
+}
+
+extern "C" {
+
+int clb_fmap_create(int device, clb_fmap** out) {
+    if (!out) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(device));
+    clb_fmap* f = new (std::nothrow) clb_fmap();
+    if (!f) return CLB_ENOMEM;
+    f->device = device; f->stream = nullptr; f->stage = nullptr; f->stage_cap = 0;
+    cudaError_t e = cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete f; return set_cuda_error(e, "fmap stream", __FILE__, __LINE__); }
+    *out = f;
+    return CLB_OK;
+}
+
+void clb_fmap_destroy(clb_fmap* f) {
+    if (!f) return;
+    cudaSetDevice(f->device);
+    for (auto& kv : f->sets) delete kv.second;
+    f->gather_tab.release();
+    if (f->stage) cudaFreeHost(f->stage);
+    if (f->stream) cudaStreamDestroy(f->stream);
+    delete f;
+}
+
+int clb_fmap_put(clb_fmap* f, uint32_t idx, const clb_keypoint* kps, const uint64_t* desc, int n) {
+    if (!f) return CLB_EINVAL;
+    int rc = put_set(f, idx, kps, desc, n, cudaMemcpyHostToDevice, f->stream);
+    if (rc) return rc;
+    CLB_CUDA(cudaStreamSynchronize(f->stream));
+    return CLB_OK;
+}
+
+int clb_fmap_put_dev(clb_fmap* f, uint32_t idx, const clb_keypoint* d_kps, const uint64_t* d_desc, int n, void* stream) {
+    if (!f) return CLB_EINVAL;
+    return put_set(f, idx, d_kps, d_desc, n, cudaMemcpyDeviceToDevice, stream ? (cudaStream_t)stream : f->stream);
+}
+
+int clb_fmap_count(const clb_fmap* f, uint32_t idx, int* n_out) {
+    if (!f || !n_out) return CLB_EINVAL;
+    const FSet* set = find_set(f, idx);
+    if (!set) { snprintf(g_err, sizeof(g_err), "feature set %u is not in the map", idx); return CLB_ENOTFOUND; }
+    *n_out = set->n;
+    return CLB_OK;
+}
+
+int clb_fmap_size(const clb_fmap* f) { return f ? (int)f->sets.size() : 0; }
+
+int clb_fmap_erase(clb_fmap* f, uint32_t idx) {
+    if (!f) return CLB_EINVAL;
+    auto it = f->sets.find(idx);
+    if (it == f->sets.end()) { snprintf(g_err, sizeof(g_err), "feature set %u is not in the map", idx); return CLB_ENOTFOUND; }
+    CLB_CUDA(cudaSetDevice(f->device));
+    delete it->second;
+    f->sets.erase(it);
+    return CLB_OK;
+}
+
+int clb_fmap_get(clb_fmap* f, uint32_t idx, clb_keypoint* kps_out, uint64_t* desc_out, int cap, int* n_out) {
+    if (!f || !n_out) return CLB_EINVAL;
+    const FSet* set = find_set(f, idx);
+    if (!set) { snprintf(g_err, sizeof(g_err), "feature set %u is not in the map", idx); return CLB_ENOTFOUND; }
+    *n_out = set->n;
+    if (set->n > cap) return CLB_ECAPACITY;
+    CLB_CUDA(cudaSetDevice(f->device));
+    if (kps_out && !set->has_kps && set->n > 0) { snprintf(g_err, sizeof(g_err), "feature set %u holds no keypoints", idx); return CLB_EINVAL; }
+    if (desc_out && set->n > 0) CLB_CUDA(cudaMemcpyAsync(desc_out, set->desc.p, (size_t)set->n * 64, cudaMemcpyDeviceToHost, f->stream));
+    if (kps_out && set->n > 0) CLB_CUDA(cudaMemcpyAsync(kps_out, set->kps.p, (size_t)set->n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, f->stream));
+    CLB_CUDA(cudaStreamSynchronize(f->stream));
+    return CLB_OK;
+}
+
+int clb_fmap_desc_dev(const clb_fmap* f, uint32_t idx, const uint64_t** d_desc_out, const clb_keypoint** d_kps_out, int* n_out) {
+    if (!f) return CLB_EINVAL;
+    const FSet* set = find_set(f, idx);
+    if (!set) { snprintf(g_err, sizeof(g_err), "feature set %u is not in the map", idx); return CLB_ENOTFOUND; }
+    if (d_desc_out) *d_desc_out = set->desc.as<uint64_t>();
+    if (d_kps_out) *d_kps_out = set->has_kps ? set->kps.as<clb_keypoint>() : nullptr;
+    if (n_out) *n_out = set->n;
+    return CLB_OK;
+}
+
+}  // extern "C"
+
+// ---- batched pair matching --------------------------------------------------------------------
+namespace {
+
+struct PairPlan {
+    std::vector<int> nQ, nT;
+    std::vector<long long> out_off;
+    long long total_rows = 0;
+    int max_nQ = 0;
+};
+
+// gather of landmark rows: 4 threads per 64-byte row
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const uint4* const* __restrict__ bases, const int2* __restrict__ list, int n, uint4* __restrict__ out) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 4ll * n) return;
+    const int2 e = list[t >> 2];
+    out[t] = __ldg(bases[e.x] + 4ll * e.y + (t & 3));
+}
+
+}  // namespace
+
+static int run_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                     int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
+    const int tpc = [&] {
+        std::vector<int> nQ(npairs), nT(npairs);
+        for (int p = 0; p < npairs; ++p) {
+            const FSet* q = find_set(f, pairs[p].query_idx);
+            const FSet* t = find_set(f, pairs[p].train_idx);
+            const int hi = pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi;
+            nQ[p] = hi - pairs[p].q_lo; nT[p] = t->n;
+        }
+        return tc_plan_pairs(nQ.data(), nT.data(), npairs, m->sm_count);
+    }();
+    // count the CTAs and the partial rows
+    size_t njobs = 0, part_rows = 0;
+    int max_nQ = 0;
+    for (int p = 0; p < npairs; ++p) {
+        const FSet* q = find_set(f, pairs[p].query_idx);
+        const FSet* t = find_set(f, pairs[p].train_idx);
+        const int nQ = (pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi) - pairs[p].q_lo;
+        if (nQ > max_nQ) max_nQ = nQ;
+        if (nQ <= 0 || t->n <= 0) continue;
+        const int tiles = (t->n + 127) / 128, chunks = (tiles + tpc - 1) / tpc;
+        njobs += (size_t)((nQ + 255) / 256) * chunks;
+        part_rows += (size_t)chunks * nQ;
+    }
+    if (njobs > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "pair list too large for one launch"); return CLB_EINVAL; }
+    const size_t tab_bytes = njobs * sizeof(TcJob) + (size_t)npairs * sizeof(MergeJob);
+    // the previous call's table copy must have left the pinned staging area before it is rewritten
+    if (m->jobs_ev_set) CLB_CUDA(cudaEventSynchronize(m->jobs_ev));
+    int rc = pinned_reserve(&m->jobs_host, &m->jobs_host_cap, tab_bytes);
+    if (rc) return rc;
+    CLB_CUDA(m->jobs.reserve(tab_bytes));
+    CLB_CUDA(m->pair_part.reserve((part_rows > 0 ? part_rows : 1) * sizeof(uint2)));
+    TcJob* tj = reinterpret_cast<TcJob*>(m->jobs_host);
+    MergeJob* mj = reinterpret_cast<MergeJob*>(tj + njobs);
+    uint2* part = m->pair_part.as<uint2>();
+    size_t j = 0, part_off = 0;
+    long long out_off = 0;
+    for (int p = 0; p < npairs; ++p) {
+        const FSet* q = find_set(f, pairs[p].query_idx);
+        const FSet* t = find_set(f, pairs[p].train_idx);
+        const int q_lo = pairs[p].q_lo;
+        const int nQ = (pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi) - q_lo;
+        const int tiles = (t->n + 127) / 128;
+        const int chunks = (nQ > 0 && t->n > 0) ? (tiles + tpc - 1) / tpc : 0;
+        MergeJob& mg = mj[p];
+        mg.partial = part + part_off;
+        mg.match = d_match + out_off;
+        mg.best = d_best ? d_best + out_off : nullptr;
+        mg.second = d_second ? d_second + out_off : nullptr;
+        mg.nQ = nQ > 0 ? nQ : 0; mg.nT = t->n; mg.nchunks = chunks; mg.rows_per_chunk = tpc * 128;
+        for (int c = 0; c < chunks; ++c) {
+            const int tile0 = c * tpc, ntiles = std::min(tpc, tiles - tile0);
+            for (int b = 0; b < (nQ + 255) / 256; ++b) {
+                TcJob& job = tj[j++];
+                job.Q = reinterpret_cast<const uint32_t*>(q->desc.as<uint64_t>() + 8ll * q_lo);
+                job.Tx = t->tx.as<uint8_t>();
+                job.partial_chunk = part + part_off + (size_t)c * nQ;
+                job.nQ = nQ; job.qblock = b; job.tile0 = tile0; job.ntiles = ntiles;
+                job.chunk_rows = std::min(ntiles * 128, t->n - tile0 * 128);
+                job._pad = 0;
+            }
+        }
+        part_off += (size_t)chunks * (nQ > 0 ? nQ : 0);
+        out_off += nQ > 0 ? nQ : 0;
+    }
+    // longest CTAs first: the hardware hands out blockIdx.x in order, so this is longest-processing-time-first packing
+    std::stable_sort(tj, tj + njobs, [](const TcJob& a, const TcJob& b) { return a.ntiles > b.ntiles; });
+    if (tab_bytes > 0) {
+        CLB_CUDA(cudaMemcpyAsync(m->jobs.p, m->jobs_host, tab_bytes, cudaMemcpyHostToDevice, s));
+        if (!m->jobs_ev_set) { CLB_CUDA(cudaEventCreateWithFlags(&m->jobs_ev, cudaEventDisableTiming)); m->jobs_ev_set = true; }
+        CLB_CUDA(cudaEventRecord(m->jobs_ev, s));
+    }
+    rc = launch_match_tc_jobs(m->jobs.as<TcJob>(), (int)njobs, s);
+    if (rc) return rc;
+    g_last_match_path = 4;
+    return launch_merge_jobs(reinterpret_cast<const MergeJob*>(m->jobs.as<TcJob>() + njobs), npairs, max_nQ, threshold, ratio, s);
+}
+
+static int check_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, long long* total_rows) {
+    if (!m || !f || npairs < 0 || (npairs > 0 && !pairs)) { snprintf(g_err, sizeof(g_err), "bad pair list"); return CLB_EINVAL; }
+    if (m->device != f->device) { snprintf(g_err, sizeof(g_err), "matcher and feature map live on different devices"); return CLB_EINVAL; }
+    long long tot = 0;
+    for (int p = 0; p < npairs; ++p) {
+        const FSet* q = find_set(f, pairs[p].query_idx);
+        const FSet* t = find_set(f, pairs[p].train_idx);
+        if (!q || !t) { snprintf(g_err, sizeof(g_err), "pair %d: feature set %u is not in the map", p, !q ? pairs[p].query_idx : pairs[p].train_idx); return CLB_ENOTFOUND; }
+        const int hi = pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi;
+        if (pairs[p].q_lo < 0 || hi < pairs[p].q_lo || hi > q->n) { snprintf(g_err, sizeof(g_err), "pair %d: query rows [%d, %d) outside the set's %d rows", p, pairs[p].q_lo, hi, q->n); return CLB_EINVAL; }
+        tot += hi - pairs[p].q_lo;
+    }
+    *total_rows = tot;
+    return CLB_OK;
+}
+
+extern "C" {
+
+int clb_match_pairs_rows(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, long long* rows_out) {
+    long long tot = 0;
+    int rc = check_pairs(m, f, pairs, npairs, &tot);
+    if (rc) return rc;
+    if (rows_out) *rows_out = tot;
+    return CLB_OK;
+}
+
+int clb_match_pairs_dev(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                        int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream) {
+    long long tot = 0;
+    int rc = check_pairs(m, f, pairs, npairs, &tot);
+    if (rc) return rc;
+    if (tot == 0) return CLB_OK;
+    if (!d_match_out) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(m->device));
+    return run_pairs(m, f, pairs, npairs, threshold < 0 ? m->o.thresh : threshold, ratio, d_match_out, d_best_out, d_second_out,
+                     stream ? (cudaStream_t)stream : m->stream);
+}
+
+int clb_match_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                    int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out) {
+    long long tot = 0;
+    int rc = check_pairs(m, f, pairs, npairs, &tot);
+    if (rc) return rc;
+    if (tot == 0) return CLB_OK;
+    if (!match_out) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(m->device));
+    CLB_CUDA(m->pair_out.reserve((size_t)tot * 12));
+    int32_t* o = m->pair_out.as<int32_t>();
+    cudaStream_t s = m->stream;
+    rc = run_pairs(m, f, pairs, npairs, threshold < 0 ? m->o.thresh : threshold, ratio, o, best_d_out ? o + tot : nullptr,
+                   second_d_out ? o + 2 * tot : nullptr, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(match_out, o, (size_t)tot * 4, cudaMemcpyDeviceToHost, s));
+    if (best_d_out) CLB_CUDA(cudaMemcpyAsync(best_d_out, o + tot, (size_t)tot * 4, cudaMemcpyDeviceToHost, s));
+    if (second_d_out) CLB_CUDA(cudaMemcpyAsync(second_d_out, o + 2 * tot, (size_t)tot * 4, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    return CLB_OK;
+}
+
+// ---- map database: setupMapDatabase (colocData.hpp:89-121) + setMapData (GPUMatcher.hpp:110-117) on the device ----
+int clb_set_map_from_fmap(clb_matcher* m, clb_fmap* f, const clb_obs* obs, int n, int* n_map_out, void* stream) {
+    if (!m || !f || n < 0 || (n > 0 && !obs)) { snprintf(g_err, sizeof(g_err), "bad observation list"); return CLB_EINVAL; }
+    if (m->device != f->device) { snprintf(g_err, sizeof(g_err), "matcher and feature map live on different devices"); return CLB_EINVAL; }
+    CLB_CUDA(cudaSetDevice(m->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
+    std::map<uint32_t, int> slot_of;
+    std::vector<const uint64_t*> bases;
+    int kept = 0;
+    for (int i = 0; i < n; ++i) {
+        if (obs[i].feat == 0xFFFFFFFFu) continue;                        // UndefinedIndexT: landmark without a feature, skipped
+        const FSet* set = find_set(f, obs[i].idx);
+        if (!set) { snprintf(g_err, sizeof(g_err), "observation %d: feature set %u is not in the map", i, obs[i].idx); return CLB_ENOTFOUND; }
+        if (obs[i].feat >= (uint32_t)set->n) { snprintf(g_err, sizeof(g_err), "observation %d: feature %u outside set %u (%d rows)", i, obs[i].feat, obs[i].idx, set->n); return CLB_EINVAL; }
+        if (slot_of.emplace(obs[i].idx, (int)bases.size()).second) bases.push_back(set->desc.as<uint64_t>());
+        ++kept;
+    }
+    const size_t base_bytes = (bases.size() * sizeof(void*) + 15) & ~(size_t)15;
+    const size_t bytes = base_bytes + (size_t)kept * sizeof(int2);
+    int rc = pinned_reserve(&f->stage, &f->stage_cap, bytes);
+    if (rc) return rc;
+    if (!bases.empty()) memcpy(f->stage, bases.data(), bases.size() * sizeof(void*));
+    int2* list = reinterpret_cast<int2*>(static_cast<char*>(f->stage) + base_bytes);
+    for (int i = 0, k = 0; i < n; ++i) {
+        if (obs[i].feat == 0xFFFFFFFFu) continue;
+        list[k++] = make_int2(slot_of[obs[i].idx], (int)obs[i].feat);
+    }
+    CLB_CUDA(f->gather_tab.reserve(bytes > 0 ? bytes : 16));
+    CLB_CUDA(m->map.reserve((size_t)(kept > 0 ? kept : 1) * 64));
+    if (kept > 0) {
+        CLB_CUDA(cudaMemcpyAsync(f->gather_tab.p, f->stage, bytes, cudaMemcpyHostToDevice, s));
+        const long long threads = 4ll * kept;
+        gather_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(
+            reinterpret_cast<const uint4* const*>(f->gather_tab.p),
+            reinterpret_cast<const int2*>(static_cast<char*>(f->gather_tab.p) + base_bytes), kept, m->map.as<uint4>());
+        CLB_LAUNCHED();
+    }
+    m->n_map = kept;
+    m->mapx_valid = false;
+    if (n_map_out) *n_map_out = kept;
+    CLB_CUDA(cudaStreamSynchronize(s));       // the pinned table may be rewritten by the next call
+    return CLB_OK;
+}
+
+}  // extern "C"

@@ -7,16 +7,7 @@
 
 using namespace clb;
 
-struct clb_matcher {
-    clb_matcher_opts o;
-    int device, sm_count;
-    cudaStream_t stream;
-    DevBuf q, t, map, scratch, out;   // out: match | best | second (3 x nQ int32)
-    DevBuf qx, tx, mapx;              // +-1 E4M3 expansions for the tensor-core path (match_tc.cu)
-    int n_map;
-    bool mapx_valid;
-    int mapx_ver;                     // kernel version the cached map expansion was made for
-};
+#include "matcher_priv.cuh"
 
 // Expand the operands when the tensor-core path applies; *Qx / *Tx stay NULL for the POPC path.
 // `map` = T is the resident map (expanded once per clb_set_map, not per query set).
@@ -83,6 +74,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     clb_matcher* m = new (std::nothrow) clb_matcher();
     if (!m) return CLB_ENOMEM;
     m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->mapx_ver = 0; m->stream = nullptr;
+    m->jobs_host = nullptr; m->jobs_host_cap = 0; m->jobs_ev_set = false;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);
@@ -97,6 +89,9 @@ void clb_matcher_destroy(clb_matcher* m) {
     cudaSetDevice(m->device);
     m->q.release(); m->t.release(); m->map.release(); m->scratch.release(); m->out.release();
     m->qx.release(); m->tx.release(); m->mapx.release();
+    m->jobs.release(); m->pair_part.release(); m->pair_out.release();
+    if (m->jobs_host) cudaFreeHost(m->jobs_host);
+    if (m->jobs_ev_set) cudaEventDestroy(m->jobs_ev);
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }

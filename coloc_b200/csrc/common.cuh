@@ -105,6 +105,24 @@ int  tc_version();
 bool tc_needs_qx();      // v1 kernel (queries staged in shared memory) wants the expanded query image too
 int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s);
+extern int g_last_match_path;
+// batched pair lists (api_fmap.cu): one v4 CTA per TcJob, one merge row block per MergeJob; operands are E2M1 images (expand4)
+struct TcJob {
+    const uint32_t* Q;        // packed query rows of the pair's slice (row 0 = first row of the slice)
+    const uint8_t* Tx;        // expanded (E2M1, pre-swizzled) image of the pair's training set
+    uint2* partial_chunk;     // partial[chunk][0 .. nQ)
+    int nQ, qblock, tile0, ntiles, chunk_rows, _pad;
+};
+struct MergeJob {
+    const uint2* partial;
+    int32_t *match, *best, *second;   // best / second may be NULL
+    int nQ, nT, nchunks, rows_per_chunk;
+};
+size_t tc4_t_bytes(int nT);
+int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s);
+int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count);      // -> DB tiles per chunk, shared by all pairs
+int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s);
+int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int threshold, float ratio, cudaStream_t s);
 // pyramid.cu
 int launch_resize(const LevelTable& lt, cudaStream_t s);   // fills levels 1..n-1 from level 0
 // fast.cu

@@ -340,6 +340,38 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
     return CLB_OK;
 }
 
+// batched merge_chunks_kernel: blockIdx.y = pair of the list
+__global__ void __launch_bounds__(256)
+merge_jobs_kernel(const MergeJob* __restrict__ jobs, int threshold, float ratio) {
+    const MergeJob j = jobs[blockIdx.y];
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= j.nQ) return;
+    int best = CLB_BEST_NONE, second = CLB_SECOND_NONE, best_i = -1;
+    for (int c = 0; c < j.nchunks; ++c) {
+        const uint2 p = j.partial[(size_t)c * j.nQ + qi];
+        if (p.x == 0xFFFFFFFFu) continue;
+        feed((int)(p.x >> MT_KEY_SHIFT), c * j.rows_per_chunk + (int)(p.x & MT_IDX_MASK), best, best_i, second);
+        feed(p.y == 0xFFFFFFFFu ? CLB_BEST_NONE : (int)(p.y >> MT_KEY_SHIFT), -1, best, best_i, second);
+    }
+    bool ok;
+    if (ratio > 0.f) ok = j.nT >= 2 && (float)best < ratio * (float)second;
+    else             ok = j.nT > 0 && (second - best > threshold);
+    j.match[qi] = ok ? best_i : CLB_NO_MATCH;
+    if (j.best) j.best[qi] = best;
+    if (j.second) j.second[qi] = second;
+}
+
+int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int threshold, float ratio, cudaStream_t s) {
+    if (njobs <= 0 || max_nQ <= 0) return CLB_OK;
+    if (njobs > 65535) { snprintf(g_err, sizeof(g_err), "too many pairs in one list"); return CLB_EINVAL; }
+    dim3 grid((max_nQ + 255) / 256, njobs);
+    timer("merge").begin(s);
+    merge_jobs_kernel<<<grid, 256, 0, s>>>(d_jobs, threshold, ratio);
+    timer("merge").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
 int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int threshold,
                           int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
     if (nQ <= 0) return CLB_OK;

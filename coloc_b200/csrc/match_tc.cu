@@ -753,9 +753,11 @@ __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0,
     tc_process32(v1, row0 + 32, st);
 }
 
-__global__ void __launch_bounds__(TC4_THREADS, 1)
-match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
-                 uint2* __restrict__ partial, int dbg) {
+// One CTA of the v4 sweep: query rows [qblock*256, +256) of Q against DB tiles [tile0, tile0+ntiles) of the expanded image Tx
+// (chunk_rows of them real); the per-query (best, second) packed keys of this chunk go to partial_chunk[query row].
+__device__ __forceinline__ void
+tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int qblock, int tile0, int ntiles, int chunk_rows,
+        uint2* __restrict__ partial_chunk, int dbg) {
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t raw = tc_smem_u32(tc_smem_raw);
     const uint32_t sB = (raw + 1023u) & ~1023u;
@@ -766,10 +768,6 @@ match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
     uint2* smem_res = reinterpret_cast<uint2*>(tc_smem_raw + (sB - raw));      // ring reused after the sweep
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
-    const int tile0 = blockIdx.y * tiles_per_chunk;
-    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
-    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
 
     if (tid == 0) {
         for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
@@ -836,7 +834,7 @@ match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
         const int e = warp - 2;
         const int quarter = warp & 3, m = (e >> 2) & 1, half = e >> 3;
         const int row = quarter * 32 + lane;
-        const int qi = blockIdx.x * TC_QROWS + m * TC_TILE + row;
+        const int qi = qblock * TC_QROWS + m * TC_TILE + row;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
         {
             uint32_t r[32];
@@ -884,7 +882,7 @@ match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
             const uint2 o = smem_res[m * TC_TILE + row];
             const uint32_t b = min(st.best, o.x);
             const uint32_t sec = min(max(st.best, o.x), min(st.second, o.y));
-            partial[(size_t)blockIdx.y * nQ + qi] = make_uint2(b, sec);
+            partial_chunk[qi] = make_uint2(b, sec);
         }
     }
 
@@ -894,6 +892,23 @@ match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
     }
+}
+
+__global__ void __launch_bounds__(TC4_THREADS, 1)
+match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                 uint2* __restrict__ partial, int dbg) {
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+    tc4_cta(Q, nQ, Tx, blockIdx.x, tile0, ntiles, chunk_rows, partial + (size_t)blockIdx.y * nQ, dbg);
+}
+
+// Batched form: one CTA per job of a device-resident job list (all pairs of a pair list in one launch).
+__global__ void __launch_bounds__(TC4_THREADS, 1)
+match_tc4_jobs_kernel(const TcJob* __restrict__ jobs) {
+    const TcJob j = jobs[blockIdx.x];
+    tc4_cta(j.Q, j.nQ, j.Tx, j.qblock, j.tile0, j.ntiles, j.chunk_rows, j.partial_chunk, 0);
 }
 
 // ---- host side --------------------------------------------------------------------------------
@@ -955,6 +970,64 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
 }
 
 bool tc_needs_qx() { return g_match_tc_ver == 1 || g_match_tc_ver == 3; }
+
+// ---- batched pair lists: always the v4 kernel on E2M1 images, whatever match_tc_ver says -------
+size_t tc4_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * TC3_TILE_BYTES; }
+
+int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s) {
+    const size_t chunks = tc4_t_bytes(n) / 16;
+    if (chunks == 0) return CLB_OK;
+    const size_t blocks = (chunks + 255) / 256;
+    if (blocks > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "descriptor set too large to expand"); return CLB_EINVAL; }
+    timer("expand").begin(s);
+    expand4_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
+    timer("expand").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+// One chunk length (in DB tiles) for every pair of the list, chosen with the same CTA cost model as tc_plan: the
+// CTA count is summed over the pairs, so small pairs fill each other's waves.
+int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count) {
+    int max_tiles = 1;
+    for (int p = 0; p < npairs; ++p) {
+        const int t = (nT[p] + TC_TILE - 1) / TC_TILE;
+        if (t > max_tiles) max_tiles = t;
+    }
+    double best_t = 1e30;
+    int best_tpc = max_tiles < TC_MAX_TILES_PER_CHUNK ? max_tiles : TC_MAX_TILES_PER_CHUNK;
+    for (int c = 1; c <= 256; ++c) {
+        int tpc = (max_tiles + c - 1) / c;
+        if (tpc > TC_MAX_TILES_PER_CHUNK) continue;
+        if (tpc < 4 && c > 1) break;
+        long long ctas = 0;
+        for (int p = 0; p < npairs; ++p) {
+            if (nQ[p] <= 0 || nT[p] <= 0) continue;
+            const long long tiles = (nT[p] + TC_TILE - 1) / TC_TILE;
+            ctas += (long long)((nQ[p] + TC_QROWS - 1) / TC_QROWS) * ((tiles + tpc - 1) / tpc);
+        }
+        const long long waves = (ctas + sm_count - 1) / sm_count;
+        const double t = (double)waves * (0.8 * tpc + 15.0);
+        if (t < best_t * 0.98) { best_t = t; best_tpc = tpc; }
+    }
+    return best_tpc > 0 ? best_tpc : 1;
+}
+
+int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s) {
+    if (njobs <= 0) return CLB_OK;
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    CLB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+        CLB_CUDA(cudaFuncSetAttribute(match_tc4_jobs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC4_SMEM_TOTAL));
+        if (dev >= 0 && dev < 64) attr_done[dev] = true;
+    }
+    timer("match").begin(s);
+    match_tc4_jobs_kernel<<<njobs, TC4_THREADS, TC4_SMEM_TOTAL, s>>>(d_jobs);
+    timer("match").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
 
 int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s) {

@@ -1,0 +1,20 @@
+// matcher_priv.cuh -- the matcher object behind the C ABI, shared by api_matcher.cu and api_fmap.cu
+#pragma once
+#include "common.cuh"
+
+struct clb_matcher {
+    clb_matcher_opts o;
+    int device, sm_count;
+    cudaStream_t stream;
+    clb::DevBuf q, t, map, scratch, out;   // out: match | best | second (3 x nQ int32)
+    clb::DevBuf qx, tx, mapx;              // +-1 expansions for the tensor-core path (match_tc.cu)
+    int n_map;
+    bool mapx_valid;
+    int mapx_ver;                          // kernel version the cached map expansion was made for
+    // pair lists (api_fmap.cu): job tables staged in pinned memory, per-chunk partials, host-call output
+    clb::DevBuf jobs, pair_part, pair_out;
+    void* jobs_host;
+    size_t jobs_host_cap;
+    cudaEvent_t jobs_ev;
+    bool jobs_ev_set;
+};

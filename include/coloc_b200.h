@@ -25,6 +25,7 @@ extern "C" {
 #define CLB_ECAPACITY     3   /* caller buffer / maxkp too small; *n_out holds the needed count */
 #define CLB_ENOMEM        4
 #define CLB_EUNSUPPORTED  5
+#define CLB_ENOTFOUND     6   /* a feature-set index that is not in the clb_fmap */
 
 #define CLB_MAX_LEVELS    16
 #define CLB_NO_MATCH      (-1)
@@ -171,6 +172,57 @@ int  clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uin
  * test: first-min-wins across parts, global second = 2nd smallest of the union.  DEVICE pointers. */
 int  clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,
                             int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
+/* ---------------------------------------------------------------- device FeatureMap ------ */
+/* SURVEY 8(f)-1/2.  The reference keeps each frame's descriptors in host Regions (coloc::FeatureMap = idx ->
+ * unique_ptr<AKAZE_Binary_Regions>, GPUDetector.hpp:167-182), uploads BOTH sets again for every pair
+ * (GPUMatcher.hpp:165-172 -> :180-226) and the gathered landmark rows for every map update (colocData.hpp:89-121 ->
+ * GPUMatcher.hpp:110-117).  A clb_fmap keeps every set on the device once (packed rows, optional keypoints and the
+ * tensor-core operand image); pair lists and the map database are then built from device memory. */
+typedef struct clb_fmap clb_fmap;
+int  clb_fmap_create(int device, clb_fmap** out);
+void clb_fmap_destroy(clb_fmap* f);
+/* regions[idx] = (kps, desc): replaces an existing entry (GPUDetector.hpp:182 `regions[idx] = std::move(...)`).
+ * kps may be NULL.  Host pointers, blocking. */
+int  clb_fmap_put(clb_fmap* f, uint32_t idx, const clb_keypoint* kps, const uint64_t* desc, int n);
+/* same from DEVICE buffers (the outputs of clb_detect_describe_dev / clb_stream_next), asynchronous on `stream`;
+ * later calls that use the entry must be ordered after it (same stream, or synchronise). */
+int  clb_fmap_put_dev(clb_fmap* f, uint32_t idx, const clb_keypoint* d_kps, const uint64_t* d_desc, int n, void* stream);
+int  clb_fmap_count(const clb_fmap* f, uint32_t idx, int* n_out);          /* CLB_ENOTFOUND when absent */
+int  clb_fmap_size(const clb_fmap* f);                                     /* number of entries */
+int  clb_fmap_erase(clb_fmap* f, uint32_t idx);
+/* copy an entry back to the host (kps_out / desc_out may be NULL); CLB_ECAPACITY with *n_out = rows when cap is short */
+int  clb_fmap_get(clb_fmap* f, uint32_t idx, clb_keypoint* kps_out, uint64_t* desc_out, int cap, int* n_out);
+/* device pointers of an entry (valid until the entry is replaced or erased) */
+int  clb_fmap_desc_dev(const clb_fmap* f, uint32_t idx, const uint64_t** d_desc_out, const clb_keypoint** d_kps_out, int* n_out);
+
+/* One pair of a pair list: query rows [q_lo, q_hi) of set query_idx against all rows of set train_idx (q_hi < 0 = to
+ * the end of the set).  Row slices are what SURVEY 8(e) shards across GPUs. */
+typedef struct clb_pair {
+    uint32_t query_idx, train_idx;
+    int32_t  q_lo, q_hi;
+} clb_pair;
+/* GPUMatcher::computeMatches(FeatureMap&, PairWiseMatches&) (GPUMatcher.hpp:143-155) for a whole pair list in ONE sweep
+ * launch + ONE merge launch.  Outputs are the per-pair match[] arrays of clb_match_2nn concatenated in list order
+ * (clb_match_pairs_rows gives the total length); match values index rows of the pair's training set.  ratio > 0
+ * applies the NNdistanceRatio test (clb_match_2nn_ratio) instead of the margin test; threshold < 0 = the matcher's
+ * own.  best / second outputs may be NULL.  Always the tensor-core kernel (match_tc_ver 4), any size. */
+int  clb_match_pairs_rows(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, long long* rows_out);
+int  clb_match_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                     int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
+/* DEVICE outputs, asynchronous on `stream` (NULL = the matcher's stream); one call in flight per matcher */
+int  clb_match_pairs_dev(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                         int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
+/* One landmark observation: feature `feat` of set `idx` (openMVG Observation::id_feat of view idx). */
+typedef struct clb_obs {
+    uint32_t idx, feat;
+} clb_obs;
+/* colocData::setupMapDatabase (colocData.hpp:89-121) + GPUMatcher::setMapData (GPUMatcher.hpp:110-117) without the host
+ * round trip: map row k = descriptor `feat` of set `idx` of the k-th observation whose feat != 0xFFFFFFFF
+ * (UndefinedIndexT entries are skipped, as the reference does); *n_map_out = rows kept.  The rows become the matcher's
+ * resident map (clb_match_map*).  CLB_ENOTFOUND / CLB_EINVAL for an unknown set / a feature outside its set. */
+int  clb_set_map_from_fmap(clb_matcher* m, clb_fmap* f, const clb_obs* obs, int n, int* n_map_out, void* stream);
 
 /* ---------------------------------------------------------------- measurement ------------ */
 /* pipe micro-benchmarks that back the match roofline: dependent-free POPC / LOP3

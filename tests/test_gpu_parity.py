@@ -428,3 +428,148 @@ def test_resident_map_dev_api(clb, oracle, tc):
         m.close(); m2.close()
     finally:
         clb.set_param("match_tc", -1)
+
+
+# ------------------------------------------------------------------ device FeatureMap, pair lists, map database
+def _ragged_sets(sizes, seed):
+    """descriptor sets that share planted rows (so pairs have real matches) plus duplicates (ties)"""
+    base = synth.random_descriptors(max(max(sizes), 8), seed)
+    sets = []
+    for k, n in enumerate(sizes):
+        if n == 0:
+            sets.append(np.zeros((0, 8), np.uint64)); continue
+        S, _ = synth.planted_queries(base, n, seed + 10 + k)
+        if n > 6:
+            S[n - 1] = S[2]                                   # duplicate rows inside a training set
+        sets.append(S)
+    return sets
+
+
+def test_fmap_put_get_erase(clb):
+    f = clb.FeatureMap()
+    d = synth.random_descriptors(300, 1)
+    k = np.zeros(300, clb.KP_DTYPE); k["x"] = np.arange(300); k["angle"] = 0.5
+    f.put(7, d, k); f.put(9, d[:5])
+    assert len(f) == 2 and 7 in f and 8 not in f and f.count(9) == 5
+    kk, dd = f.get(7, want_kps=True)
+    assert np.array_equal(dd, d) and np.array_equal(kk, k)
+    f.put(7, d[:11])                                          # regions[idx] is replaced, not appended to
+    assert f.count(7) == 11 and np.array_equal(f.get(7), d[:11])
+    f.put(3, np.zeros((0, 8), np.uint64)); assert f.count(3) == 0 and f.get(3).shape == (0, 8)
+    with pytest.raises(clb.ClbError) as e:
+        f.count(1234)
+    assert e.value.code == 6
+    with pytest.raises(clb.ClbError):
+        f.get(9, want_kps=True)                               # stored without keypoints
+    f.erase(9); assert 9 not in f
+    with pytest.raises(clb.ClbError):
+        f.erase(9)
+    f.close()
+
+
+@pytest.mark.parametrize("sizes", [(0, 1, 5, 130, 257, 1000), (3000, 2177, 4100), (129, 128, 127, 1)])
+def test_match_pairs_vs_oracle(clb, oracle, sizes):
+    sets = _ragged_sets(sizes, 40 + len(sizes))
+    f = clb.FeatureMap(); m = clb.Matcher(maxkp=16)
+    for i, S in enumerate(sets):
+        f.put(100 + i, S)
+    n = len(sets)
+    pairs = [(100 + i, 100 + j) for i in range(n) for j in range(n)]       # includes self pairs (distance 0 / duplicates)
+    for thr in (40, 0):
+        got = m.match_pairs(f, pairs, thr, want_dist=True)
+        for k, (qi, ti) in enumerate(pairs):
+            Q, T = sets[qi - 100], sets[ti - 100]
+            if len(Q) == 0:
+                assert len(got[0][k]) == 0; continue
+            if len(T) == 0:
+                assert (got[0][k] == -1).all(); continue
+            ref = oracle.match_2nn(Q, T, thr)
+            for name, a, b in zip(("match", "best", "second"), (got[0][k], got[1][k], got[2][k]), ref):
+                assert np.array_equal(a, b), (thr, qi, ti, name, int((a != b).sum()))
+    assert clb.get_param("last_match_path") == 4
+    m.close(); f.close()
+
+
+def test_match_pairs_row_slices_and_ratio(clb, oracle):
+    """query-row slices (what SURVEY 8e shards over GPUs) concatenate to the full pair; ratio mode equals clb_match_2nn_ratio"""
+    sets = _ragged_sets((2500, 1800, 900), 77)
+    f = clb.FeatureMap(); m = clb.Matcher(maxkp=4096)
+    for i, S in enumerate(sets):
+        f.put(i, S)
+    full = m.match_pairs(f, [(0, 1), (2, 0)], 40)
+    cut = m.match_pairs(f, [(0, 1, 0, 700), (0, 1, 700, 701), (0, 1, 701, 2500), (2, 0, 0, 0), (2, 0, 0, 900)], 40)
+    assert np.array_equal(np.concatenate(cut[:3]), full[0]) and len(cut[3]) == 0 and np.array_equal(cut[4], full[1])
+    assert np.array_equal(full[0], oracle.match_2nn(sets[0], sets[1], 40)[0])
+    r = m.match_pairs(f, [(1, 2)], ratio=0.8, want_dist=True)
+    one = m.compute_matches_ratio(sets[1], sets[2], 0.8, want_dist=True)
+    assert all(np.array_equal(r[i][0], one[i]) for i in range(3))
+    with pytest.raises(clb.ClbError):
+        m.match_pairs(f, [(0, 5)], 40)                        # unknown set
+    with pytest.raises(clb.ClbError):
+        m.match_pairs(f, [(0, 1, 10, 5000)], 40)              # rows outside the set
+    m.close(); f.close()
+
+
+def test_match_pairs_config3_equals_pairwise_calls(clb):
+    """config 3 shape: 4 views of one scene, the 12 ordered pairs in one launch == 12 clb_match_2nn calls (themselves oracle-checked above)"""
+    import torch
+    views, _ = synth.config_views(1280, 720, 4)
+    det = clb.Detector(1280, 720, maxkp=120000); m = clb.Matcher(maxkp=30000); f = clb.FeatureMap()
+    descs = []
+    for k, v in enumerate(views):
+        kp, d = det.detect_and_describe(v)
+        descs.append(d.copy()); f.put(k, d, kp)
+    pairs = [(i, j) for i in range(4) for j in range(4) if i != j]
+    got = m.match_pairs(f, pairs, 40)
+    for k, (i, j) in enumerate(pairs):
+        assert np.array_equal(got[k], m.compute_matches(descs[i], descs[j], 40)), (i, j)
+    # device outputs, caller's stream
+    tot = m.pair_rows(f, pairs)
+    out = torch.full((tot,), -7, dtype=torch.int32, device="cuda")
+    m.match_pairs_dev(f, pairs, 40, out, stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), np.concatenate(got))
+    det.close(); m.close(); f.close()
+
+
+def test_fmap_put_dev_from_detector(clb):
+    """device hand-off: detect+describe on the device, rows go into the FeatureMap without touching the host"""
+    import torch
+    img = synth.config_frame(1280, 720, 5)
+    det = clb.Detector(1280, 720, maxkp=60000); f = clb.FeatureMap()
+    kp, d = det.detect_and_describe(img)
+    dk = torch.from_numpy(kp.view(np.uint8).copy()).cuda(); dd = torch.from_numpy(d.view(np.int64).copy()).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    f.put_dev(4, dd, len(d), dk, stream=st)
+    torch.cuda.synchronize()
+    kk, d2 = f.get(4, want_kps=True)
+    assert np.array_equal(d2, d) and kk.tobytes() == kp.tobytes()
+    det.close(); f.close()
+
+
+def test_set_map_from_fmap(clb, oracle):
+    """setupMapDatabase + setMapData as a device gather: map rows in observation order, UndefinedIndexT skipped"""
+    rng = np.random.default_rng(3)
+    sets = _ragged_sets((1200, 800, 50), 11)
+    f = clb.FeatureMap(); m = clb.Matcher(maxkp=4096)
+    for i, S in enumerate(sets):
+        f.put(10 * i, S)
+    n_obs = 5000
+    idx = rng.integers(0, 3, n_obs)
+    feat = np.array([rng.integers(0, len(sets[i])) for i in idx], np.int64)
+    undef = rng.random(n_obs) < 0.1
+    feat[undef] = clb.UNDEFINED_FEAT
+    n_map = m.set_map_from_fmap(f, np.stack([idx * 10, feat], 1))
+    keep = ~undef
+    M = np.stack([sets[i][ft] for i, ft in zip(idx[keep], feat[keep])])
+    assert n_map == len(M)
+    Q, _ = synth.planted_queries(M, 700, 5)
+    got = m.match_with_map(Q, 60, want_dist=True)
+    ref = oracle.match_2nn(Q, M, 60)
+    assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+    assert m.set_map_from_fmap(f, np.zeros((0, 2), np.int64)) == 0
+    with pytest.raises(clb.ClbError):
+        m.set_map_from_fmap(f, [(10, 800)])                   # feature outside set 10 (800 rows)
+    with pytest.raises(clb.ClbError):
+        m.set_map_from_fmap(f, [(11, 0)])                     # unknown set
+    m.close(); f.close()
