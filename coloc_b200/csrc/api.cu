@@ -98,6 +98,7 @@ const char* clb_strerror(int code) {
         case CLB_ENOMEM: return "out of device memory";
         case CLB_EUNSUPPORTED: return "unsupported";
         case CLB_ENOTFOUND: return "feature set not found";
+        case CLB_EIO: return "file i/o failed";
         default: return "unknown error";
     }
 }

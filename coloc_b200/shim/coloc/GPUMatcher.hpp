@@ -33,7 +33,12 @@ public:
         clbCheck(clb_matcher_create(&o, 0, &m), "clb_matcher_create");
     }
     ~GPUMatcher() { freeGPUMemory(); }
-    void freeGPUMemory() { if (m) clb_matcher_destroy(m); m = nullptr; }          // :102-108
+    void freeGPUMemory() {                                                          // :102-108
+        if (fmap) clb_fmap_destroy(fmap);
+        fmap = nullptr;
+        if (m) clb_matcher_destroy(m);
+        m = nullptr;
+    }
 
     void setMapData(int kpNum, void* desc) {                                        // :110-117
         clbCheck(clb_set_map(m, static_cast<const uint64_t*>(desc), kpNum), "clb_set_map");
@@ -48,15 +53,34 @@ public:
     }
 
     // all unordered pairs I<J (Utils::handlePairs -> exhaustivePairs, Pair_Builder.hpp:25-33)   :143-155
+    // The reference uploads both descriptor sets again for every pair (:188-196); here every Regions goes to the device
+    // FeatureMap once and the whole pair list is one clb_match_pairs call (one sweep launch + one merge launch).
     T computeMatches(FeatureMap& regions, PairWiseMatches& putativeMatches) {
         const int numImages = static_cast<int>(regions.size());
+        if (!fmap) clbCheck(clb_fmap_create(0, &fmap), "clb_fmap_create");
+        std::vector<int> count((size_t)numImages);
+        for (int i = 0; i < numImages; ++i) {
+            auto& r = regions.at((openMVG::IndexT)i);
+            count[i] = (int)r->RegionCount();
+            clbCheck(clb_fmap_put(fmap, (uint32_t)i, nullptr, static_cast<const uint64_t*>(r->DescriptorRawData()), count[i]), "clb_fmap_put");
+        }
+        std::vector<clb_pair> pairs;
+        size_t rows = 0;
         for (int i = 0; i < numImages; ++i)
             for (int j = i + 1; j < numImages; ++j) {
-                const Pair pairIdx(i, j);
-                IndMatches pairMatches;
-                computeMatchesPair(pairIdx, regions, pairMatches);
-                if (!pairMatches.empty()) putativeMatches.insert({pairIdx, std::move(pairMatches)});
+                clb_pair p; p.query_idx = (uint32_t)i; p.train_idx = (uint32_t)j; p.q_lo = 0; p.q_hi = -1;
+                pairs.push_back(p); rows += (size_t)count[i];
             }
+        h_matches.resize(rows);
+        clbCheck(clb_match_pairs(m, fmap, pairs.data(), (int)pairs.size(), 40, 0.f, h_matches.data(), nullptr, nullptr), "clb_match_pairs");
+        size_t off = 0;
+        for (const clb_pair& p : pairs) {
+            IndMatches pairMatches;
+            for (int q = 0; q < count[p.query_idx]; ++q)
+                if (h_matches[off + q] != -1) pairMatches.emplace_back(q, h_matches[off + q]);
+            off += (size_t)count[p.query_idx];
+            if (!pairMatches.empty()) putativeMatches.insert({Pair(p.query_idx, p.train_idx), std::move(pairMatches)});
+        }
         return EXIT_SUCCESS;
     }
 
@@ -70,6 +94,25 @@ public:
         putativeMatches = computeMatches(const_cast<void*>(regions[pairIdx.first]->DescriptorRawData()),
                                          const_cast<void*>(regions[pairIdx.second]->DescriptorRawData()),
                                          (int)regions[pairIdx.first]->RegionCount(), (int)regions[pairIdx.second]->RegionCount());
+    }
+
+    // The CPU build's pair matcher (CPUMatcher::computeMatchesPair, CPUMatcher.hpp:67-76 -> matching::DistanceRatioMatch):
+    // ratio test, IndMatch dedup and (x,y) dedup, with the 2-NN search on the GPU.  IndMatch(i_ = idx in pair.first, j_ = idx in pair.second).
+    T computeMatchesPairRatio(const Pair& pairIdx, FeatureMap& regions, IndMatches& putativeMatches, float distRatio = 0.8f) {
+        const auto& rI = regions.at(pairIdx.first);
+        const auto& rJ = regions.at(pairIdx.second);
+        const int nI = (int)rI->RegionCount(), nJ = (int)rJ->RegionCount();
+        std::vector<float> fI((size_t)4 * nI), fJ((size_t)4 * nJ);
+        for (int k = 0; k < nI; ++k) { fI[4 * k] = rI->Features()[k].x(); fI[4 * k + 1] = rI->Features()[k].y(); }
+        for (int k = 0; k < nJ; ++k) { fJ[4 * k] = rJ->Features()[k].x(); fJ[4 * k + 1] = rJ->Features()[k].y(); }
+        std::vector<uint32_t> out((size_t)2 * (nJ > 0 ? nJ : 1));
+        int n = 0;
+        clbCheck(clb_distance_ratio_match(m, static_cast<const uint64_t*>(rI->DescriptorRawData()), fI.data(), nI,
+                                          static_cast<const uint64_t*>(rJ->DescriptorRawData()), fJ.data(), nJ, distRatio,
+                                          out.data(), nJ > 0 ? nJ : 1, &n), "clb_distance_ratio_match");
+        putativeMatches.clear();
+        for (int k = 0; k < n; ++k) putativeMatches.emplace_back(out[2 * k], out[2 * k + 1]);
+        return EXIT_SUCCESS;
     }
 
     void matchSceneWithMap(int& droneId, colocData& data, IndMatches& mapMatches) {                                     // :174-178
@@ -111,6 +154,7 @@ public:
 
 private:
     clb_matcher* m = nullptr;
+    clb_fmap* fmap = nullptr;      // device-side copy of the FeatureMap used by computeMatches(FeatureMap&, ...)
     unsigned int kpTrain = 0, kpQuery = 0, kpMap = 0;
     uint8_t matchThreshold;
     std::vector<uint64_t> train, query;

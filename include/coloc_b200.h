@@ -26,6 +26,7 @@ extern "C" {
 #define CLB_ENOMEM        4
 #define CLB_EUNSUPPORTED  5
 #define CLB_ENOTFOUND     6   /* a feature-set index that is not in the clb_fmap */
+#define CLB_EIO           7   /* a .feat / .desc file could not be opened, read or written */
 
 #define CLB_MAX_LEVELS    16
 #define CLB_NO_MATCH      (-1)
@@ -223,6 +224,30 @@ typedef struct clb_obs {
  * (UndefinedIndexT entries are skipped, as the reference does); *n_map_out = rows kept.  The rows become the matcher's
  * resident map (clb_match_map*).  CLB_ENOTFOUND / CLB_EINVAL for an unknown set / a feature outside its set. */
 int  clb_set_map_from_fmap(clb_matcher* m, clb_fmap* f, const clb_obs* obs, int n, int* n_map_out, void* stream);
+
+/* ---------------------------------------------------------------- host side of the path -- */
+/* Region packing of GPUDetector::detectFeaturesFile (GPUDetector.hpp:167-182): feats_out[4k..4k+3] =
+ * SIOPointFeature{1.2^s * x, 1.2^s * y, 7 * 1.2^s, angle} of keypoint k (1.2f hard-coded there, float pow).  HOST. */
+int  clb_pack_regions(const clb_keypoint* kps, int n, float* feats_out);
+/* Binary_Regions<SIOPointFeature,64>::Save / Load (binary_regions.hpp:51-66): `.feat` = one "x y scale orientation" text line
+ * per region (feature.hpp:168-182, default ostream float format), `.desc` = size_t count + count x 64 raw bytes
+ * (descriptor.hpp:165-210).  Either path may be NULL to skip that file.  HOST. */
+int  clb_regions_save(const char* feat_path, const char* desc_path, const float* feats, const uint64_t* desc, int n);
+int  clb_regions_count(const char* desc_path, long long* n_out);
+/* CLB_ECAPACITY with *n_out = rows in the file when cap is short; CLB_EINVAL when the two files disagree in length */
+int  clb_regions_load(const char* feat_path, const char* desc_path, float* feats_out, uint64_t* desc_out, int cap, int* n_out);
+/* Tail of matching::DistanceRatioMatch (regions_matcher.hpp:166-181) on a match[] array (match[q] = database row or -1):
+ * (database idx, query idx) pairs -> IndMatch::getDeduplicated -> IndMatchDecorator<float>::getDeduplicated over the
+ * (x, y) of both sides; feats* = positions with `stride*` floats per region (x, y first).  Output order = the reference's
+ * (iteration order of its std::set).  HOST, no GPU.  CLB_ECAPACITY with *n_out = needed pairs. */
+int  clb_dedup_matches(const int32_t* match, int nQ, const float* featsI, int strideI, const float* featsJ, int strideJ,
+                       uint32_t* pairs_out, int cap, int* n_out);
+/* matching::DistanceRatioMatch(ratio, BRUTE_FORCE_HAMMING, regions_I, regions_J, out) as the CPU build calls it
+ * (CPUMatcher.hpp:58-89): regions_I is the database, regions_J the queries; GPU 2-NN + ratio test, host dedup.
+ * feats = 4 floats per region (clb_pack_regions layout).  pairs_out = (i_, j_) pairs. */
+int  clb_distance_ratio_match(clb_matcher* m, const uint64_t* descI, const float* featsI, int nI,
+                              const uint64_t* descJ, const float* featsJ, int nJ, float ratio,
+                              uint32_t* pairs_out, int cap, int* n_out);
 
 /* ---------------------------------------------------------------- measurement ------------ */
 /* pipe micro-benchmarks that back the match roofline: dependent-free POPC / LOP3

@@ -272,3 +272,26 @@ def ref_gpu_k2nn(Q, T, threshold, iters=1):
     rc = ref_gpu().ref_gpu_k2nn(_p(Q, _u64p), len(Q), _p(T, _u64p), len(T), int(threshold), _p(m, _i32p), int(iters), C.byref(ms))
     assert rc == 0
     return m, ms.value
+
+
+def ref_regions_save(feat_path, desc_path, feats, desc):
+    """the reference's Binary_Regions::Save (compiled from its sources); returns True on success"""
+    f = np.ascontiguousarray(feats, np.float32).reshape(-1, 4); d = np.ascontiguousarray(desc, np.uint64).reshape(-1, 8)
+    return ref_cpu().ref_regions_save(_p(f, _f32p), d.ctypes.data_as(_u8p), len(d), str(feat_path).encode(), str(desc_path).encode()) == 0
+
+
+def ref_regions_load(feat_path, desc_path, cap):
+    f = np.zeros((cap, 4), np.float32); d = np.zeros((cap, 8), np.uint64)
+    nd = C.c_int(0)
+    n = ref_cpu().ref_regions_load(str(feat_path).encode(), str(desc_path).encode(), _p(f, _f32p), d.ctypes.data_as(_u8p), cap, C.byref(nd))
+    return (None, None) if n < 0 else (f[:n], d[:nd.value])
+
+
+def ref_distance_ratio_match(desc_i, feats_i, desc_j, feats_j, ratio=0.8):
+    """the reference's matching::DistanceRatioMatch (regions_matcher.cpp:19-30) on two AKAZE_Binary_Regions; (k, 2) uint32"""
+    di = np.ascontiguousarray(desc_i, np.uint64).reshape(-1, 8); dj = np.ascontiguousarray(desc_j, np.uint64).reshape(-1, 8)
+    fi = np.ascontiguousarray(feats_i, np.float32).reshape(-1, 4); fj = np.ascontiguousarray(feats_j, np.float32).reshape(-1, 4)
+    out = np.zeros((max(1, len(dj)), 2), np.uint32)
+    n = ref_cpu().ref_distance_ratio_match(_p(fi, _f32p), di.ctypes.data_as(_u8p), len(di), _p(fj, _f32p), dj.ctypes.data_as(_u8p), len(dj),
+                                           C.c_float(ratio), out.ctypes.data_as(C.c_void_p), len(out))
+    return out[:n]

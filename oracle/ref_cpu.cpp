@@ -6,6 +6,8 @@
 //   * ArrayMatcherBruteForce<uchar,Hamming<uchar>> + NNdistanceRatio
 //       lib/openMVG/src/openMVG/matching/matcher_brute_force.hpp:100-200, metric_hamming.hpp:80-99,
 //       matching_filters.hpp:39-60  (what CPUMatcher.hpp:67-76 -> regions_matcher.hpp:137-184 runs)
+//   * matching::DistanceRatioMatch on two AKAZE_Binary_Regions (regions_matcher.cpp:19-30: ratio filter,
+//       IndMatch dedup, (x,y) dedup) and Binary_Regions::Save / Load (.feat / .desc, binary_regions.hpp:51-66)
 #include <cstring>
 #include <thread>
 #include <future>
@@ -20,6 +22,11 @@
 #include "openMVG/matching/matcher_brute_force.hpp"
 #include "openMVG/matching/metric_hamming.hpp"
 #include "openMVG/matching/matching_filters.hpp"
+#include "openMVG/features/feature.hpp"
+#include "openMVG/features/descriptor.hpp"
+#include "openMVG/features/binary_regions.hpp"
+#include "openMVG/features/regions_factory.hpp"
+#include "openMVG/matching/regions_matcher.hpp"
 
 static_assert(sizeof(Keypoint) == 20, "Keypoint.h layout");
 
@@ -65,6 +72,49 @@ int ref_bruteforce_2nn(const uint8_t* T, int nT, const uint8_t* Q, int nQ, float
         for (int i : ok) ratio_ok[i] = 1;
     }
     return 0;
+}
+
+static void fill_regions(openMVG::features::AKAZE_Binary_Regions& r, const float* feats, const uint8_t* desc, int n) {
+    r.Features().resize(n); r.Descriptors().resize(n);
+    for (int i = 0; i < n; ++i) {
+        r.Features()[i] = openMVG::features::SIOPointFeature(feats[4 * i], feats[4 * i + 1], feats[4 * i + 2], feats[4 * i + 3]);
+        std::memcpy(&r.Descriptors()[i], desc + 64 * (size_t)i, 64);
+    }
+}
+
+// Binary_Regions<SIOPointFeature,64>::Save: feats = n x (x, y, scale, orientation), desc = n x 64 B.  0 = ok.
+int ref_regions_save(const float* feats, const uint8_t* desc, int n, const char* feat_path, const char* desc_path) {
+    openMVG::features::AKAZE_Binary_Regions r;
+    fill_regions(r, feats, desc, n);
+    return r.Save(feat_path, desc_path) ? 0 : 1;
+}
+
+// Binary_Regions::Load; returns the region count (or -1), copies at most cap rows out
+int ref_regions_load(const char* feat_path, const char* desc_path, float* feats, uint8_t* desc, int cap, int* n_desc) {
+    openMVG::features::AKAZE_Binary_Regions r;
+    if (!r.Load(feat_path, desc_path)) return -1;
+    const int n = (int)r.Features().size();
+    if (n_desc) *n_desc = (int)r.Descriptors().size();
+    for (int i = 0; i < n && i < cap; ++i) {
+        const auto& f = r.Features()[i];
+        feats[4 * i] = f.x(); feats[4 * i + 1] = f.y(); feats[4 * i + 2] = f.scale(); feats[4 * i + 3] = f.orientation();
+    }
+    for (int i = 0; i < (int)r.Descriptors().size() && i < cap; ++i) std::memcpy(desc + 64 * (size_t)i, &r.Descriptors()[i], 64);
+    return n;
+}
+
+// matching::DistanceRatioMatch(ratio, BRUTE_FORCE_HAMMING, regions_I (database), regions_J (queries), out) exactly as
+// CPUMatcher.hpp:67-76 calls it.  out = (i_, j_) pairs; returns the number of matches (may exceed cap).
+int ref_distance_ratio_match(const float* featsI, const uint8_t* descI, int nI, const float* featsJ, const uint8_t* descJ, int nJ,
+                             float ratio, uint32_t* out, int cap) {
+    openMVG::features::AKAZE_Binary_Regions a, b;
+    fill_regions(a, featsI, descI, nI);
+    fill_regions(b, featsJ, descJ, nJ);
+    openMVG::matching::IndMatches m;
+    openMVG::matching::DistanceRatioMatch(ratio, openMVG::matching::BRUTE_FORCE_HAMMING, a, b, m);
+    int n = 0;
+    for (const auto& x : m) { if (n < cap) { out[2 * n] = x.i_; out[2 * n + 1] = x.j_; } ++n; }
+    return n;
 }
 
 int ref_hw_threads() { return (int)std::thread::hardware_concurrency(); }

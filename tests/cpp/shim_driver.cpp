@@ -46,6 +46,10 @@ int main(int argc, char** argv) {
     openMVG::matching::PairWiseMatches putative;
     if (matcher.computeMatches(regions, putative) != EXIT_SUCCESS) return 4;
     dump(f, putative[{0, 1}]);
+    // the CPU build's semantics (ratio + dedups) on the same pair
+    openMVG::matching::IndMatches ratioMatches;
+    if (matcher.computeMatchesPairRatio({0, 1}, regions, ratioMatches) != EXIT_SUCCESS) return 5;
+    dump(f, ratioMatches);
     // map tracking: vehicle 0's descriptors as the "map", vehicle 1 as the frame
     matcher.setMapData((int)regions[0]->RegionCount(), const_cast<void*>(regions[0]->DescriptorRawData()));
     colocData data; data.regions = std::move(regions);

@@ -56,6 +56,7 @@ def test_shim_matches_oracle(tmp_path, clb, oracle):
     kb, off = _read_vec(buf, off, clb.KP_DTYPE); db, off = _read_vec(buf, off, np.uint64)
     feats, off = _read_vec(buf, off, np.dtype([("x", "<f4"), ("y", "<f4"), ("s", "<f4"), ("o", "<f4")]))
     pair, off = _read_vec(buf, off, np.dtype([("i", "<u4"), ("j", "<u4")]))
+    ratm, off = _read_vec(buf, off, np.dtype([("i", "<u4"), ("j", "<u4")]))
     mapm, off = _read_vec(buf, off, np.dtype([("i", "<u4"), ("j", "<u4")]))
     oka, oda = oracle.detect_describe(a); okb, odb = oracle.detect_describe(b)
     for k, ok in ((ka, oka), (kb, okb)):
@@ -75,3 +76,8 @@ def test_shim_matches_oracle(tmp_path, clb, oracle):
     mm = oracle.match_2nn(odb, oda, 60)[0]
     q = np.nonzero(mm >= 0)[0]
     assert np.array_equal(mapm["i"], mm[q]) and np.array_equal(mapm["j"], q)
+    # CPU-build semantics: the reference's own DistanceRatioMatch on the same regions (when oracle/_ref travelled here)
+    if oracle.ref_cpu() is not None and hasattr(oracle.ref_cpu(), "ref_distance_ratio_match"):
+        from coloc_b200 import regions as R
+        ref = oracle.ref_distance_ratio_match(oda, R.pack_regions(oka), odb, R.pack_regions(okb), 0.8)
+        assert np.array_equal(np.stack([ratm["i"], ratm["j"]], 1), ref)

@@ -40,3 +40,26 @@ assert np.array_equal(dist[:, 0], b) and np.array_equal(dist[:, 1], s)
 np.savez_compressed(os.path.join(GOLD, "match_small.npz"), Q=Q, T=T, threshold=40, match=m, best=b, second=s,
                     ratio_ok=ok)
 print("match_small:", int((m >= 0).sum()), "matches of", len(Q))
+
+# ---- host side: .feat/.desc written by the REFERENCE's Binary_Regions::Save, and DistanceRatioMatch's dedup tail
+from coloc_b200 import regions as R, KP_DTYPE
+rng = np.random.default_rng(5)
+k = np.zeros(64, KP_DTYPE)
+k["x"] = rng.integers(3, 637, 64); k["y"] = rng.integers(3, 477, 64); k["scale"] = rng.integers(0, 8, 64)
+k["angle"] = rng.uniform(-np.pi, np.pi, 64).astype(np.float32)
+feats = R.pack_regions(k); feats[3] = (1e-7, 123456.789, 3.0e10, -0.0)
+desc = synth.random_descriptors(64, 6)
+fp, dp = os.path.join(GOLD, "regions_small.feat"), os.path.join(GOLD, "regions_small.desc")
+assert O.ref_regions_save(fp, dp, feats, desc)
+fl, dl = O.ref_regions_load(fp, dp, 100)
+assert np.array_equal(dl, desc)
+np.savez_compressed(os.path.join(GOLD, "regions_small.npz"), feats=feats, desc=desc, feats_loaded=fl)
+
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from test_host_regions import _dedup_case
+dI, fI, dJ, fJ = _dedup_case(9, gx=60, gy=45)
+idx, dist, ok = O.ref_bruteforce_2nn(dI, dJ, 0.8)
+match = np.where(ok.astype(bool), idx[:, 0], -1).astype(np.int32)
+pairs = O.ref_distance_ratio_match(dI, fI, dJ, fJ, 0.8)
+np.savez_compressed(os.path.join(GOLD, "regions_dedup.npz"), match=match, feats_i=fI, feats_j=fJ, pairs=pairs)
+print("regions_dedup:", int((match >= 0).sum()), "ratio matches ->", len(pairs), "after dedup")
