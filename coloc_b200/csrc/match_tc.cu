@@ -61,6 +61,15 @@ __device__ __forceinline__ void tc_mbar_expect_tx(uint32_t bar, uint32_t bytes) 
 __device__ __forceinline__ void tc_mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// non-blocking phase test
+__device__ __forceinline__ bool tc_mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
 // bounded wait: a protocol bug traps (launch error) instead of hanging the GPU
 __device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok, spins = 0;
@@ -72,6 +81,18 @@ __device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity) {
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
         if (ok) return;
         if ((++spins & 1023u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 8000000000ll) __trap();
+        }
+    }
+}
+// latency-critical wait: spins on the non-suspending test (a suspended try_wait is woken late)
+__device__ __forceinline__ void tc_mbar_spin(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    long long t0 = 0;
+    while (!tc_mbar_test(bar, parity)) {
+        if ((++spins & 4095u) == 0) {
             const long long now = clock64();
             if (t0 == 0) t0 = now;
             else if (now - t0 > 8000000000ll) __trap();
@@ -697,7 +718,7 @@ match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restri
         for (int j = 0; j < ntiles; ++j) {
             tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
             tc_fence_after();
-            if (dbg == 1) {
+            if (dbg == 1 || dbg == 4 || dbg == 5) {
                 tc_fence_before(); __syncwarp();
                 if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
                 continue;
@@ -723,7 +744,8 @@ match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restri
 // merged by packed key at the end (exact: min of the bests, second smallest of the four).  The queries sit in TMEM
 // (columns 320-447, 8 E2M1 per 32-bit column), so shared memory is a 14-stage DB ring again.
 static constexpr int TC4_EPI_WARPS = 16;
-static constexpr int TC4_THREADS = 32 * (2 + TC4_EPI_WARPS);
+static constexpr int TC4_MMA1_WARP = 2 + TC4_EPI_WARPS;                 // second MMA-issuing warp comes after the epilogue warps
+static constexpr int TC4_THREADS = 32 * (3 + TC4_EPI_WARPS);
 static constexpr int TC4_STAGES = 14;
 static constexpr int TC4_SMEM_B = TC4_STAGES * TC_KB_BYTES;
 static constexpr int TC4_SMEM_TOTAL = TC4_SMEM_B + TC2_SMEM_BAR + 1024;
@@ -755,6 +777,13 @@ __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0,
 
 // One CTA of the v4 sweep: query rows [qblock*256, +256) of Q against DB tiles [tile0, tile0+ntiles) of the expanded image Tx
 // (chunk_rows of them real); the per-query (best, second) packed keys of this chunk go to partial_chunk[query row].
+//
+// Warp roles: 0 = TMA producer; 1 and 18 = MMA issue for query tile 0 / 1 (each accumulator's chain has its own issuing
+// warp: tcgen05.mma issue is nearly synchronous -- the queue behind the tensor pipe is ~2 instructions deep -- so a single
+// issuing warp lets the pipe drain at every barrier wait; with two, one warp's waits are covered by the other's MMAs:
+// 1 450 -> see profiles/r1_ncu_summary.md cycles per DB tile against the 1 029 of a bare MMA stream); 2..17 = epilogue.
+// dbg (timing experiments, results are garbage unless 0 or 7): 1 no TMEM reads, 2 TMEM reads without the reduction,
+// 3 no MMAs, 7 normal sweep + real SM clock printed by a few CTAs.
 __device__ __forceinline__ void
 tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int qblock, int tile0, int ntiles, int chunk_rows,
         uint2* __restrict__ partial_chunk, int dbg) {
@@ -768,9 +797,11 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     uint2* smem_res = reinterpret_cast<uint2*>(tc_smem_raw + (sB - raw));      // ring reused after the sweep
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    long long dbg_c0 = 0; unsigned long long dbg_t0 = 0;
+    if ((dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0) { dbg_c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0)); }
 
     if (tid == 0) {
-        for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, TC_QTILES); }
         tc_mbar_init(bar_a, TC4_EPI_WARPS);
         for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC4_EPI_WARPS / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -789,7 +820,19 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
 
     if (warp == 0) {
         const uint8_t* tsrc = Tx + (size_t)tile0 * TC3_TILE_BYTES;
-        const int nit = ntiles * TC3_KB;
+        if (dbg == 18 || dbg == 19) {      // timing experiment: TMA fill of the ring at the sweep's rate, paced by the clock, nobody waits on it
+            const long long t0 = clock64();
+            for (int it = 0; it < ntiles * TC3_KB; ++it) {
+                while (clock64() - t0 < 515ll * it) { }
+                const int s = it % TC4_STAGES;
+                if (tc_elect_one()) {
+                    tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
+                    tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+                }
+                __syncwarp();
+            }
+        }
+        const int nit = dbg >= 10 && dbg != 20 ? 0 : ntiles * TC3_KB;
         for (int it = 0; it < nit; ++it) {
             const int s = it % TC4_STAGES;
             tc_mbar_wait(bar_empty + 8 * s, (uint32_t)(((it / TC4_STAGES) & 1) ^ 1));
@@ -799,36 +842,100 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             }
             __syncwarp();
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == TC4_MMA1_WARP) {
+        const int m = warp == 1 ? 0 : 1;
         tc_mbar_wait(bar_a, 0);
         tc_fence_after();
         const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
-        for (int j = 0; j < ntiles; ++j) {
+        const uint32_t d0 = tmem + (uint32_t)(m * TC_TILE);
+        if (dbg >= 10 && dbg != 20) {     // timing experiments on a bare MMA stream (warp 1 only): 10 nothing else, 11 + a commit, 12 + a wait on a
+                             // completed barrier, 13 + fence::after_thread_sync, 14 + elect per MMA group of 4
+            if (m == 0 && (dbg < 15 || dbg >= 17)) {
+                for (int j = 0; j < ntiles; ++j) {
 #pragma unroll
-            for (int m = 0; m < TC_QTILES; ++m) {
+                    for (int g = 0; g < 4; ++g) {
+                        if (dbg == 12) tc_mbar_wait(bar_a, 0);
+                        if (dbg == 13) tc_fence_after();
+                        if (tc_elect_one()) {
+                            const uint64_t b0 = desc_hi | (uint64_t)(((sB + ((2 * j + (g & 1)) % TC4_STAGES) * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+#pragma unroll
+                            if (dbg == 17 || dbg == 18) {
+                                const uint64_t a0 = desc_hi | (uint64_t)(((sB + ((2 * j + (g & 1) + 7) % TC4_STAGES) * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+#pragma unroll
+                                for (int k = 0; k < 4; ++k)
+                                    tc_mma_mxf4(tmem + (uint32_t)((g >> 1) * TC_TILE), a0 + (uint64_t)(k * 2), b0 + (uint64_t)(k * 2), (uint32_t)(((g & 1) | k) != 0), tm_sf, tm_sf + 32u);
+                            } else {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                tc_mma_mxf4_ts(tmem + (uint32_t)((g >> 1) * TC_TILE), tm_a + (uint32_t)(g * 32 + k * 8), b0 + (uint64_t)(k * 2), (uint32_t)(((g & 1) | k) != 0), tm_sf, tm_sf + 32u);
+                            }
+                            if (dbg == 11) tc_commit(bar_tfull + 8);
+                        }
+                        __syncwarp();
+                    }
+                }
+                if (tc_elect_one()) tc_commit(bar_tfull);
+                __syncwarp();
+                tc_mbar_wait(bar_tfull, 0);
+            }
+        } else if (dbg == 8) {      // timing experiment: where the issuing warp's time goes (clock64 around each section)
+            long long t_te = 0, t_fu = 0, t_is = 0, t_fx = 0, c0 = clock64();
+            for (int j = 0; j < ntiles; ++j) {
                 tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
                 tc_fence_after();
+                long long c1 = clock64(); t_te += c1 - c0; c0 = c1;
 #pragma unroll
                 for (int kb = 0; kb < TC3_KB; ++kb) {
                     const int it = j * TC3_KB + kb;
                     const int s = it % TC4_STAGES;
-                    if (m == 0) {
-                        tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC4_STAGES) & 1));
-                        tc_fence_after();
-                    }
+                    tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC4_STAGES) & 1));
+                    c1 = clock64(); t_fu += c1 - c0; c0 = c1;
+                    tc_mbar_wait(bar_a, 0);                            // completed long ago: the fixed cost of a wait
+                    c1 = clock64(); t_fx += c1 - c0; c0 = c1;
                     if (tc_elect_one()) {
                         const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
                         const uint32_t a0 = tm_a + (uint32_t)(m * 64 + kb * 32);
-                        const uint32_t d0 = tmem + (uint32_t)(m * TC_TILE);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0), tm_sf, tm_sf + 32u);
-                        if (m == TC_QTILES - 1) tc_commit(bar_empty + 8 * s);
+                        tc_commit(bar_empty + 8 * s);
                         if (kb == TC3_KB - 1) tc_commit(bar_tfull + 8 * m);
                     }
                     __syncwarp();
+                    c1 = clock64(); t_is += c1 - c0; c0 = c1;
                 }
             }
+            if (lane == 0 && qblock == 0 && tile0 == 0)
+                printf("tc4 mma warp %d: per tile  wait tempty %.1f  wait full %.1f  ready-barrier wait %.1f  issue %.1f cycles\n", m, (double)t_te / ntiles, (double)t_fu / ntiles, (double)t_fx / ntiles, (double)t_is / ntiles);
+        } else {
+        // The issuing thread is blocked while its MMAs execute and nothing is queued behind them, so every instruction
+        // between two MMAs is tensor-pipe idle time: the operand barriers are checked BEFORE the accumulator hand-off wait
+        // (which has to be sat out anyway) and the tile's 8 MMAs then go out back to back.
+        for (int j = 0; j < ntiles; ++j) {
+            const int it0 = j * TC3_KB, s0 = it0 % TC4_STAGES, s1 = (it0 + 1) % TC4_STAGES;
+            tc_mbar_wait(bar_full + 8 * s0, (uint32_t)((it0 / TC4_STAGES) & 1));
+            tc_mbar_wait(bar_full + 8 * s1, (uint32_t)(((it0 + 1) / TC4_STAGES) & 1));
+            const uint64_t b0 = desc_hi | (uint64_t)(((sB + s0 * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t b1 = desc_hi | (uint64_t)(((sB + s1 * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+            const uint32_t a0 = tm_a + (uint32_t)(m * 64);
+            if (dbg == 20) tc_mbar_spin(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
+            else           tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
+            tc_fence_after();
+            if (tc_elect_one()) {
+                if (dbg != 3) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        tc_mma_mxf4_ts(d0, a0 + (uint32_t)(32 + k * 8), b1 + (uint64_t)(k * 2), 1u, tm_sf, tm_sf + 32u);
+                }
+                tc_commit(bar_tfull + 8 * m);
+                tc_commit(bar_empty + 8 * s0);
+                tc_commit(bar_empty + 8 * s1);
+            }
+            __syncwarp();
+        }
         }
     } else {
         const int e = warp - 2;
@@ -860,12 +967,37 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         }
         const uint32_t tbase = lane_base + (uint32_t)(m * TC_TILE + half * 64);
         TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
-        for (int j = 0; j < ntiles; ++j) {
-            tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
+        if (dbg == 15 || dbg == 16) {      // timing experiment: bare TMEM read stream (16: only query tile 0's warps)
+            float acc = 0.f;
+            if (dbg == 15 || m == 0)
+                for (int j = 0; j < ntiles; ++j) {
+                    float v0[32], v1[32];
+                    tc_ld32(tbase, v0); tc_ld32(tbase + 32, v1);
+                    tc_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) acc += v0[i] + v1[i];
+                }
+            if (acc == 12345.678f) st.best = 0u;
+        }
+        for (int j = 0; j < (dbg >= 10 && dbg != 20 ? 0 : ntiles); ++j) {
+            if (dbg == 20) tc_mbar_spin(bar_tfull + 8 * m, (uint32_t)(j & 1));
+            else           tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
             tc_fence_after();
             if (dbg == 1) {
                 tc_fence_before(); __syncwarp();
                 if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                continue;
+            }
+            if (dbg == 2) {
+                float v0[32], v1[32];
+                tc_ld32(tbase, v0); tc_ld32(tbase + 32, v1);
+                tc_wait_ld();
+                tc_fence_before(); __syncwarp();
+                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                float acc = 0.f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc += v0[i] + v1[i];
+                if (acc == 12345.678f) st.best = 0u;
                 continue;
             }
             const int valid = chunk_rows - j * TC_TILE - half * 64;       // rows of this half that exist
@@ -891,6 +1023,12 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+    if ((dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0 && qblock == 0 && tile0 == 0) {     // real SM clock while the sweep runs: cycles / globaltimer ns
+        unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        const long long c1 = clock64();
+        printf("tc4 qblock %d: %lld cycles in %llu ns = %.0f MHz, %d tiles, %.1f cycles/tile\n", qblock, c1 - dbg_c0, t1 - dbg_t0,
+               1e3 * (double)(c1 - dbg_c0) / (double)(t1 - dbg_t0), ntiles, (double)(c1 - dbg_c0) / ntiles);
     }
 }
 
