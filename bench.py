@@ -491,19 +491,25 @@ def run_ours(args, rank, world, local_rank):
                         "so frac > 1 is legitimate; HBM traffic is ~0.2 % of peak", "pipes": pipes}
     else:
         peaks = measured_peaks()
-        bf16 = peaks.get("bf16_tflops")                        # burst figure: the kernel keeps 1965 MHz (+-1 operands)
+        bf16 = peaks.get("bf16_tflops")
         mult = 4.0 if path >= 3 else 2.0                       # fp4 (kind::mxf4) issues at 4x, fp8 at 2x the bf16 rate
-        peak_tf = mult * bf16 if bf16 else mult * 1590.0
+        # Denominator: the tensor pipe's issue rate for this kind at the GPU's max SM clock -- one M128 N128 K64 (fp4) or K32 (fp8)
+        # tcgen05.mma per 64 cycles per SM (B300_MICROARCH.md "tcgen05 floor"; a bare stream of this kernel's MMAs runs at
+        # 64.3 cycles each: tools/tc_dbg.py match_tc_dbg=10).  MEASURED_PEAKS.json only holds a bf16 cuBLAS figure taken
+        # under the 1 kW power cap at ~1.36 GHz; 4x (2x) that figure is reported beside it -- this kernel's +-1 operands
+        # draw ~400 W and run at ~1.84 GHz, so it exceeds that number.
+        sm_count = int(pipes.get("sm_count", 148)); max_mhz = float(clocks.get("sm_max_mhz") or 1965.0)
+        mac_per_clk = 16384.0 if path >= 3 else 8192.0
+        peak_tf = 2.0 * mac_per_clk * sm_count * max_mhz * 1e6 / 1e12
         ach_tf = 1024.0 * cmp_s_kernel / 1e12
         roof = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
                 "traffic": None, "kernel": {1: "clb::match_tc_kernel", 2: "clb::match_tc2_kernel", 3: "clb::match_tc3_kernel",
                                             4: "clb::match_tc4_kernel"}[path], "kernel_ms": k_ms,
-                "peak_source": (f"{mult:.0f} x MEASURED_PEAKS.json bf16_tflops (fp8 issues at 2x, fp4 at 4x the bf16 rate; no fp8/fp4 figure is measured)"
-                                if bf16 else f"{mult:.0f} x 1590 TFLOP/s fallback (B200_PROFILING.md)"),
+                "peak_source": f"tensor-pipe issue rate: {mac_per_clk:.0f} MAC/clk/SM x {sm_count} SMs x {max_mhz:.0f} MHz (max SM clock); "
+                               "MEASURED_PEAKS.json has no fp8/fp4 figure, see vs_measured_bf16",
+                "vs_measured_bf16": {"bf16_tflops": bf16, "multiplier": mult, "frac": (ach_tf / (mult * bf16)) if bf16 else None,
+                                     "note": "bf16_tflops is cuBLAS under the 1 kW power cap (SM ~1.36 GHz); > 1 is possible for a kernel that is not power-capped"},
                 "frac_of_nominal": ach_tf / (9000.0 if path >= 3 else 4500.0),
-                "frac_note": "the measured bf16 figure is cuBLAS under the 1 kW power cap (SM ~1.36 GHz); this kernel's +-1 operands draw ~400 W and "
-                             "hold 1965 MHz, so frac against 4x that figure flatters it: ncu (profiles/r1_ncu_summary.md) has the tensor pipe 65 % active, "
-                             "and frac_of_nominal (9 PFLOP/s dense fp4) is the conservative reading",
                 "popc_roofline": {"achieved": popc_ach, "peak": pipes["popc_gops"], "unit": "G POPC32/s", "frac": popc_frac,
                                   "note": "north_star's roofline: 16 POPC32 per comparison against the measured POPC pipe; "
                                           "the tensor-core formulation is what lets frac exceed 1"},

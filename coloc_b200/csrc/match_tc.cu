@@ -1089,7 +1089,7 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
         best_c = g_match_tc_chunks < max_chunks ? g_match_tc_chunks : max_chunks;
         if (best_c < min_chunks) best_c = min_chunks;
     } else {
-        // time model (tools/tc_small.py): a CTA costs ~0.8 us per DB tile plus ~15 us of prologue and epilogue warm-up
+        // time model (tools/tc_small.py): a CTA costs ~0.62 us per DB tile plus ~15 us of prologue and epilogue warm-up
         // (every query's threshold starts open), and the busiest SM runs `waves` CTAs back to back
         double best_t = 1e30;
         for (int c = best_c; c <= max_chunks; ++c) {
@@ -1097,7 +1097,7 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
             const int real_c = (total_tiles + tpc - 1) / tpc;
             const long long ctas = (long long)qblocks * real_c;
             const long long waves = (ctas + sm_count - 1) / sm_count;
-            const double t = (double)waves * (0.8 * tpc + 15.0);
+            const double t = (double)waves * (0.62 * tpc + 15.0);
             if (t < best_t * 0.98) { best_t = t; best_c = c; }
         }
     }
@@ -1145,7 +1145,7 @@ int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count) {
             ctas += (long long)((nQ[p] + TC_QROWS - 1) / TC_QROWS) * ((tiles + tpc - 1) / tpc);
         }
         const long long waves = (ctas + sm_count - 1) / sm_count;
-        const double t = (double)waves * (0.8 * tpc + 15.0);
+        const double t = (double)waves * (0.62 * tpc + 15.0);
         if (t < best_t * 0.98) { best_t = t; best_tpc = tpc; }
     }
     return best_tpc > 0 ? best_tpc : 1;
