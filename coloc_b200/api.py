@@ -271,6 +271,16 @@ class Matcher:
         _check(lib().clb_match_partial_dev(self._h, _dptr(dQ), int(nQ), _dptr(dT), int(nT), C.c_int64(int(t_base)),
                                            _dptr(d_partial), _sarg(stream)))
 
+    def match_partial_hostdb(self, dQ, nQ, T_host, nT, t_base, d_partial, stream=None):
+        """DB rows in (pinned) HOST memory streamed in slices behind the sweep; T_host: numpy array, torch CPU tensor or address"""
+        if isinstance(T_host, np.ndarray):
+            tp = C.c_void_p(T_host.ctypes.data)
+        elif isinstance(T_host, int):
+            tp = C.c_void_p(T_host)
+        else:
+            tp = C.c_void_p(T_host.data_ptr())
+        _check(lib().clb_match_partial_hostdb(self._h, _dptr(dQ), int(nQ), tp, int(nT), C.c_int64(int(t_base)), _dptr(d_partial), _sarg(stream)))
+
     def set_map_dev(self, dM, nM, stream=None):
         """device-resident map / DB shard (copied D2D once, expanded once for the tensor-core path)"""
         _check(lib().clb_set_map_dev(self._h, _dptr(dM), int(nM), _sarg(stream)))

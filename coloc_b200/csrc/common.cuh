@@ -95,6 +95,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
                  const void* Qx = nullptr, const void* Tx = nullptr);   // expanded operands -> tensor-core path
 int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int threshold,
                           int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s);
+int launch_fold_partials(const clb_partial* parts, int nparts, int nQ, clb_partial* out, cudaStream_t s);
 // match_tc.cu -- tcgen05 path: +-1 E4M3 expansion of the packed rows, then a tensor-core distance sweep
 bool   tc_wanted(int nQ, int nT);
 size_t tc_q_bytes(int nQ);

@@ -252,6 +252,22 @@ merge_partials_kernel(const clb_partial* __restrict__ parts, int nparts, int nQ,
     if (second_out) second_out[qi] = second;
 }
 
+// several partial arrays [part][nQ] (ascending t_base) folded into one partial array: the slices of a streamed DB
+__global__ void __launch_bounds__(256)
+fold_partials_kernel(const clb_partial* __restrict__ parts, int nparts, int nQ, clb_partial* __restrict__ out) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nQ) return;
+    int best = CLB_BEST_NONE, second = CLB_SECOND_NONE, best_i = -1;
+    for (int p = 0; p < nparts; ++p) {
+        const clb_partial v = parts[(size_t)p * nQ + qi];
+        if (v.best_i < 0) continue;
+        feed(v.best_d, v.best_i, best, best_i, second);
+        feed(v.second_d, -1, best, best_i, second);
+    }
+    clb_partial o; o.best_d = best; o.best_i = best_i; o.second_d = second; o._pad = 0;
+    out[qi] = o;
+}
+
 // ---- host side ------------------------------------------------------------------------------
 struct MatchPlan { int rq, qblocks, nchunks, rpc; };
 
@@ -368,6 +384,13 @@ int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int thresho
     timer("merge").begin(s);
     merge_jobs_kernel<<<grid, 256, 0, s>>>(d_jobs, threshold, ratio);
     timer("merge").end(s);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
+int launch_fold_partials(const clb_partial* parts, int nparts, int nQ, clb_partial* out, cudaStream_t s) {
+    if (nQ <= 0) return CLB_OK;
+    fold_partials_kernel<<<(nQ + 255) / 256, 256, 0, s>>>(parts, nparts, nQ, out);
     CLB_LAUNCHED();
     return CLB_OK;
 }

@@ -17,4 +17,9 @@ struct clb_matcher {
     size_t jobs_host_cap;
     cudaEvent_t jobs_ev;
     bool jobs_ev_set;
+    // host-resident DB streamed in slices (clb_match_partial_hostdb): ping-pong raw / expanded slice buffers, per-slice partials
+    cudaStream_t copy_stream;
+    clb::DevBuf sraw[2], sx[2], sparts, sfold;
+    cudaEvent_t ev_copied[2], ev_rawfree[2], ev_entry;
+    bool stream_ready;
 };

@@ -169,6 +169,13 @@ int  clb_match_2nn_ratio(clb_matcher* m, const uint64_t* Q, int nQ, const uint64
  * global indices start at t_base; d_partial_out[nQ] (device).  Enqueue only. */
 int  clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT,
                            int64_t t_base, clb_partial* d_partial_out, void* stream);
+/* As clb_match_partial_dev with the DB rows in HOST memory: they are copied in slices (the first of "match_slice_rows"
+ * rows, default 524 288, each next one 4x larger) on a second stream while earlier slices are expanded and swept, so the H2D copy hides behind the
+ * sweep; pinned host memory overlaps, pageable memory works but copies synchronously.  Queries and output on the DEVICE;
+ * asynchronous on `stream`: T_host must stay valid until that stream is synchronised.  clb_match_2nn (all host) takes the
+ * same path for DBs larger than one slice.  Bit-identical to the unsliced scan (slices fold in ascending row order). */
+int  clb_match_partial_hostdb(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* T_host, int nT,
+                              int64_t t_base, clb_partial* d_partial_out, void* stream);
 /* merge `nparts` partial arrays laid out [part][nQ] (ascending t_base order) and apply the margin
  * test: first-min-wins across parts, global second = 2nd smallest of the union.  DEVICE pointers. */
 int  clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,

@@ -573,3 +573,38 @@ def test_set_map_from_fmap(clb, oracle):
     with pytest.raises(clb.ClbError):
         m.set_map_from_fmap(f, [(11, 0)])                     # unknown set
     m.close(); f.close()
+
+
+@pytest.mark.parametrize("tc", [1, 0])
+def test_streamed_host_db_equals_oracle(clb, oracle, tc):
+    """DB rows streamed from host memory in slices (clb_match_partial_hostdb, and clb_match_2nn above one slice): the slices fold
+    in row order, so duplicates across slice borders still resolve to the first row"""
+    import torch
+    clb.set_param("match_tc", tc); clb.set_param("match_slice_rows", 1024)
+    try:
+        nt, nq = 5000, 700
+        T = synth.random_descriptors(nt, 31); Q, _ = synth.planted_queries(T, nq, 32)
+        T[4100] = T[50]; T[1024] = T[1023]; Q[0] = T[50]; Q[1] = T[1023]     # ties across slice borders
+        ref = oracle.match_2nn(Q, T, 40)
+        m = clb.Matcher(maxkp=4096)
+        got = m.compute_matches(Q, T, 40, want_dist=True)                    # host API, 2 slices (1024 + 3976 rows)
+        assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+        dQ = torch.from_numpy(Q.view(np.int64)).cuda()
+        Tp = torch.from_numpy(T.view(np.int64)).pin_memory()
+        part = torch.zeros((nq, 4), dtype=torch.int32, device="cuda"); out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        for _ in range(2):                                                   # second call reuses the slice buffers
+            m.match_partial_hostdb(dQ, nq, Tp, nt, 0, part, stream=st)
+            m.merge_partials_dev(part, 1, nq, 40, out[0], out[1], out[2], stream=st)
+            torch.cuda.synchronize()
+            assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
+        # two host-resident shards with global row bases, merged like the multi-GPU path
+        parts = torch.zeros((2, nq, 4), dtype=torch.int32, device="cuda")
+        m.match_partial_hostdb(dQ, nq, Tp[:2600], 2600, 0, parts[0], stream=st)
+        m.match_partial_hostdb(dQ, nq, Tp[2600:], nt - 2600, 2600, parts[1], stream=st)
+        m.merge_partials_dev(parts, 2, nq, 40, out[0], out[1], out[2], stream=st)
+        torch.cuda.synchronize()
+        assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
+        m.close()
+    finally:
+        clb.set_param("match_tc", -1); clb.set_param("match_slice_rows", 524288)
