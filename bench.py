@@ -248,6 +248,44 @@ def c2_cpu_baseline(O, synth):
             "note": "fast_nms excludes the orientation pass when the reference KFAST is timed (featureAngle is <2 % of it)"}
 
 
+def residuals_extra(clb, torch, O):
+    """the Errors() pass of AC-RANSAC for a batch of hypotheses (clb_model_residuals) against the reference's own
+    functors on one host core (ACRANSAC evaluates them serially): 2048 hypotheses x 8192 matches, symmetric epipolar + homography."""
+    rng = np.random.default_rng(5)
+    n, nh = 8192, 2048
+    x1 = rng.uniform([0, 0], [1280, 720], (n, 2)); x2 = x1 + rng.normal(0, 2.0, (n, 2))
+    out = {"matches": n, "hypotheses": nh}
+    m = clb.Matcher(maxkp=16)
+    for kind, name in ((1, "symmetric_epipolar"), (3, "homography")):
+        Ms = rng.normal(0, 1e-3, (nh, 3, 3)) + (np.eye(3) if kind == 3 else 0)
+        dM = torch.from_numpy(Ms).cuda(); d1 = torch.from_numpy(x1).cuda(); d2 = torch.from_numpy(x2).cuda()
+        dinl = torch.zeros(nh, dtype=torch.int32, device="cuda"); dres = torch.empty((nh, n), dtype=torch.float64, device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        r = {}
+        for label, res in (("counts_only", None), ("residual_matrix", dres)):
+            for _ in range(3):
+                m.model_residuals_dev(kind, dM, nh, d1, d2, n, 4.0, res, dinl, stream=st)
+            torch.cuda.synchronize()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                m.model_residuals_dev(kind, dM, nh, d1, d2, n, 4.0, res, dinl, stream=st)
+            e1.record(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 10
+            r[label] = {"ms": ms, "residuals_per_s": nh * n / (ms * 1e-3)}
+        r["residual_matrix"]["GBps_written"] = nh * n * 8 / (r["residual_matrix"]["ms"] * 1e-3) / 1e9
+        t0 = time.perf_counter(); m.model_residuals(kind, Ms, x1, x2, 4.0, want_residuals=False); r["host_in_counts_out_ms"] = (time.perf_counter() - t0) * 1e3
+        if O is not None and O.ref_cpu() is not None and hasattr(O.ref_cpu(), "ref_model_residuals"):
+            t0 = time.perf_counter()
+            for h in range(64):
+                O.ref_model_residuals(kind, Ms[h], x1, x2)
+            dt = time.perf_counter() - t0
+            r["cpu_reference"] = {"residuals_per_s": 64 * n / dt, "cores": 1, "sample": "64 hypotheses"}
+        out[name] = r
+    m.close()
+    return out
+
+
 def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
     """throughput mode (clb_stream_*): `nframes` frames of w x h from pinned host memory, up to 3 in flight; per frame the
     keypoints + descriptors come back to pinned host memory and, with_match, frame k is matched against frame k-1 on the
@@ -564,6 +602,10 @@ def run_ours(args, rank, world, local_rank):
             line["extra"]["c2_pipeline"] = c2_extra(clb, torch, synth)
         except Exception as e:   # the headline number must still print
             line["extra"]["c2_pipeline_error"] = repr(e)
+        try:
+            line["extra"]["c2_model_residuals"] = residuals_extra(clb, torch, O)
+        except Exception as e:
+            line["extra"]["c2_model_residuals_error"] = repr(e)
         for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
                        ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
             try:

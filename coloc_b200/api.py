@@ -331,6 +331,22 @@ class Matcher:
         _check(lib().clb_match_pairs_dev(self._h, fmap._h, _ptr(a), len(a), int(threshold), C.c_float(ratio),
                                          _dptr(d_match), _dptr(d_best), _dptr(d_second), _sarg(stream)))
 
+    def model_residuals(self, kind, models, x1, x2, threshold=0.0, want_residuals=True):
+        """Errors() of the AC-RANSAC kernel adaptors for a batch of hypotheses (clb_model_residuals).
+        models: (H, 3, 3) row-major float64; x1, x2: (n, 2) float64.  Returns (residuals (H, n) or None, inlier counts (H,))."""
+        M = np.ascontiguousarray(models, np.float64).reshape(-1, 9)
+        a = np.ascontiguousarray(x1, np.float64).reshape(-1, 2); b = np.ascontiguousarray(x2, np.float64).reshape(-1, 2)
+        if len(a) != len(b):
+            raise ValueError("x1 and x2 differ in length")
+        res = np.zeros((len(M), len(a)), np.float64) if want_residuals else None
+        inl = np.zeros(len(M), np.int32)
+        _check(lib().clb_model_residuals(self._h, int(kind), _ptr(M), len(M), _ptr(a), _ptr(b), len(a), C.c_double(threshold), _ptr(res), _ptr(inl)))
+        return res, inl
+
+    def model_residuals_dev(self, kind, d_models, n_models, d_x1, d_x2, n, threshold, d_res=None, d_inl=None, stream=None):
+        _check(lib().clb_model_residuals_dev(self._h, int(kind), _dptr(d_models), int(n_models), _dptr(d_x1), _dptr(d_x2), int(n),
+                                             C.c_double(threshold), _dptr(d_res), _dptr(d_inl), _sarg(stream)))
+
     def set_map_from_fmap(self, fmap, obs, stream=None):
         """colocData::setupMapDatabase (colocData.hpp:89-121) + setMapData as a device gather: obs = [(set idx, feature id)],
         entries with feature id UNDEFINED_FEAT are skipped.  Returns the number of map rows."""

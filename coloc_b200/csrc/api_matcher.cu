@@ -168,7 +168,7 @@ void clb_matcher_destroy(clb_matcher* m) {
         cudaStreamDestroy(m->copy_stream);
     }
     for (int b = 0; b < 2; ++b) { m->sraw[b].release(); m->sx[b].release(); }
-    m->sparts.release(); m->sfold.release();
+    m->sparts.release(); m->sfold.release(); m->geo.release();
     if (m->stream) cudaStreamDestroy(m->stream);
     delete m;
 }

@@ -20,6 +20,7 @@ struct clb_matcher {
     // host-resident DB streamed in slices (clb_match_partial_hostdb): ping-pong raw / expanded slice buffers, per-slice partials
     cudaStream_t copy_stream;
     clb::DevBuf sraw[2], sx[2], sparts, sfold;
+    clb::DevBuf geo;                       // clb_model_residuals staging (geometry.cu)
     cudaEvent_t ev_copied[2], ev_rawfree[2], ev_entry;
     bool stream_ready;
 };

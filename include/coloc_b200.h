@@ -256,6 +256,23 @@ int  clb_distance_ratio_match(clb_matcher* m, const uint64_t* descI, const float
                               const uint64_t* descJ, const float* featsJ, int nJ, float ratio,
                               uint32_t* pairs_out, int cap, int* n_out);
 
+/* ---------------------------------------------------------------- geometric pre-filter --- */
+/* SURVEY 8(f)-4.  The Errors() pass of the AC-RANSAC kernel adaptors (robust_estimator_ACRansacKernelAdaptator.hpp:93-99,
+ * 244-252) that RobustMatcher::filterFundamental / filterEssential / filterHomography (RobustMatcher.hpp:128-239) run per
+ * hypothesis, for a batch of hypotheses.  models: n_models x 9 doubles, ROW-major 3x3; x1, x2: n x 2 doubles (the matched
+ * positions of view 1 / view 2); residuals_out: n_models x n doubles or NULL; inliers_out[h] = #{residual < threshold} or NULL.
+ * kind: 0 EpipolarDistanceError, 1 SymmetricEpipolarDistanceError, 2 SampsonError (solver_fundamental_kernel.cpp:156-192),
+ * 3 homography AsymmetricError (solver_homography_kernel.hpp:59-63).  fp64; agrees with the reference's functors to 1e-9
+ * relative (FMA contraction differs).  Hypothesis solvers and the a-contrario selection stay on the host. */
+#define CLB_RES_EPIPOLAR            0
+#define CLB_RES_SYMMETRIC_EPIPOLAR  1
+#define CLB_RES_SAMPSON             2
+#define CLB_RES_HOMOGRAPHY          3
+int  clb_model_residuals(clb_matcher* m, int kind, const double* models, int n_models, const double* x1, const double* x2, int n,
+                         double threshold, double* residuals_out, int32_t* inliers_out);
+int  clb_model_residuals_dev(clb_matcher* m, int kind, const double* d_models, int n_models, const double* d_x1, const double* d_x2,
+                             int n, double threshold, double* d_residuals_out, int32_t* d_inliers_out, void* stream);
+
 /* ---------------------------------------------------------------- measurement ------------ */
 /* pipe micro-benchmarks that back the match roofline: dependent-free POPC / LOP3
  * streams and a mixed stream; results in ops per clock per SM and the SM clock seen.

@@ -295,3 +295,24 @@ def ref_distance_ratio_match(desc_i, feats_i, desc_j, feats_j, ratio=0.8):
     n = ref_cpu().ref_distance_ratio_match(_p(fi, _f32p), di.ctypes.data_as(_u8p), len(di), _p(fj, _f32p), dj.ctypes.data_as(_u8p), len(dj),
                                            C.c_float(ratio), out.ctypes.data_as(C.c_void_p), len(out))
     return out[:n]
+
+
+_f64p = C.POINTER(C.c_double)
+
+
+def model_residuals(kind, model, x1, x2):
+    """restatement of the reference's two-view error functors; model: 3x3 (row-major), x1 / x2: (n, 2) float64"""
+    M = np.ascontiguousarray(model, np.float64).reshape(9); a = np.ascontiguousarray(x1, np.float64).reshape(-1, 2)
+    b = np.ascontiguousarray(x2, np.float64).reshape(-1, 2)
+    out = np.zeros(len(a), np.float64)
+    lib().orc_model_residuals(int(kind), _p(M, _f64p), _p(a, _f64p), _p(b, _f64p), len(a), _p(out, _f64p))
+    return out
+
+
+def ref_model_residuals(kind, model, x1, x2):
+    """the reference's own functors (compiled from openMVG), same layout"""
+    M = np.ascontiguousarray(model, np.float64).reshape(9); a = np.ascontiguousarray(x1, np.float64).reshape(-1, 2)
+    b = np.ascontiguousarray(x2, np.float64).reshape(-1, 2)
+    out = np.zeros(len(a), np.float64)
+    ref_cpu().ref_model_residuals(int(kind), _p(M, _f64p), _p(a, _f64p), _p(b, _f64p), len(a), _p(out, _f64p))
+    return out

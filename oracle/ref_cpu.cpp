@@ -8,6 +8,8 @@
 //       matching_filters.hpp:39-60  (what CPUMatcher.hpp:67-76 -> regions_matcher.hpp:137-184 runs)
 //   * matching::DistanceRatioMatch on two AKAZE_Binary_Regions (regions_matcher.cpp:19-30: ratio filter,
 //       IndMatch dedup, (x,y) dedup) and Binary_Regions::Save / Load (.feat / .desc, binary_regions.hpp:51-66)
+//   * the two-view error functors AC-RANSAC evaluates per hypothesis (solver_fundamental_kernel.cpp:156-192,
+//       solver_homography_kernel.hpp:59-63)
 #include <cstring>
 #include <thread>
 #include <future>
@@ -27,6 +29,8 @@
 #include "openMVG/features/binary_regions.hpp"
 #include "openMVG/features/regions_factory.hpp"
 #include "openMVG/matching/regions_matcher.hpp"
+#include "openMVG/multiview/solver_fundamental_kernel.hpp"
+#include "openMVG/multiview/solver_homography_kernel.hpp"
 
 static_assert(sizeof(Keypoint) == 20, "Keypoint.h layout");
 
@@ -115,6 +119,22 @@ int ref_distance_ratio_match(const float* featsI, const uint8_t* descI, int nI, 
     int n = 0;
     for (const auto& x : m) { if (n < cap) { out[2 * n] = x.i_; out[2 * n + 1] = x.j_; } ++n; }
     return n;
+}
+
+// the reference's own error functors (solver_fundamental_kernel.cpp:156-192, solver_homography_kernel.hpp:59-63); model row-major
+void ref_model_residuals(int kind, const double* model, const double* x1, const double* x2, int n, double* out) {
+    using namespace openMVG;
+    Mat3 M;
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) M(r, c) = model[3 * r + c];
+    for (int i = 0; i < n; ++i) {
+        const Vec2 a(x1[2 * i], x1[2 * i + 1]), b(x2[2 * i], x2[2 * i + 1]);
+        switch (kind) {
+            case 0: out[i] = fundamental::kernel::EpipolarDistanceError::Error(M, a, b); break;
+            case 1: out[i] = fundamental::kernel::SymmetricEpipolarDistanceError::Error(M, a, b); break;
+            case 2: out[i] = fundamental::kernel::SampsonError::Error(M, a, b); break;
+            default: out[i] = homography::kernel::AsymmetricError::Error(M, a, b); break;
+        }
+    }
 }
 
 int ref_hw_threads() { return (int)std::thread::hardware_concurrency(); }

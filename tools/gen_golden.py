@@ -63,3 +63,14 @@ match = np.where(ok.astype(bool), idx[:, 0], -1).astype(np.int32)
 pairs = O.ref_distance_ratio_match(dI, fI, dJ, fJ, 0.8)
 np.savez_compressed(os.path.join(GOLD, "regions_dedup.npz"), match=match, feats_i=fI, feats_j=fJ, pairs=pairs)
 print("regions_dedup:", int((match >= 0).sum()), "ratio matches ->", len(pairs), "after dedup")
+
+# ---- two-view residuals from the REFERENCE's own functors (oracle/_ref), 4 error models
+from test_geometry import scene, hypotheses
+x1, x2, Hm, rng = scene(400, 3)
+out = {"x1": x1, "x2": x2}
+for kind in range(4):
+    Ms = hypotheses(kind, Hm, rng, 4)
+    out[f"models{kind}"] = Ms
+    out[f"res{kind}"] = np.stack([O.ref_model_residuals(kind, M, x1, x2) for M in Ms])
+np.savez_compressed(os.path.join(GOLD, "residuals.npz"), **out)
+print("residuals:", {k: v.shape for k, v in out.items() if k.startswith("res")})
