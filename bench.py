@@ -194,8 +194,10 @@ def c2_extra(clb, torch, synth):
     st = {k: clb.last_kernel_ms(k) for k in ("resize", "fast", "describe")}
     n = len(ka)
     ts = []
-    for it in range(10):
-        t0 = time.perf_counter(); det.detect_and_describe(img_host); ts.append(time.perf_counter() - t0)
+    clb.set_timing(False)                      # the per-kernel event pairs are not part of the user-facing call
+    for it in range(20):
+        t0 = time.perf_counter(); det.detect_and_describe(img_host, copy=False); ts.append(time.perf_counter() - t0)
+    clb.set_timing(True)
     e2e_ms = 1e3 * float(np.median(ts))
     ws, hs, _ = det.level_dims(w, h)
     pyr_bytes = sum(x * y for x, y in zip(ws, hs))

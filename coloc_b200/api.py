@@ -148,15 +148,20 @@ class Detector:
         _check(lib().clb_detector_level_dims(self._h, w, h, _ptr(ws), _ptr(hs), _ptr(fs)))
         return ws.tolist(), hs.tolist(), fs
 
-    def detect_and_describe(self, img, cap=None):
+    def detect_and_describe(self, img, cap=None, copy=True):
         """GPUDetector::detectAndDescribe (GPUDetector.hpp:216-291) on a host uint8 image."""
         img = np.ascontiguousarray(img, np.uint8)
         h, w = img.shape
         cap = cap if cap is not None else self.opts.maxkp
-        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 8), np.uint64)
+        if getattr(self, "_cap", -1) != cap:      # output buffers are kept across calls (no 10 MB allocation + zero fill per frame)
+            self._kbuf = np.empty(cap, KP_DTYPE); self._dbuf = np.empty((cap, 8), np.uint64); self._cap = cap
         n = C.c_int(0)
-        _check(lib().clb_detect_describe(self._h, _ptr(img), w, h, img.strides[0], _ptr(kps), _ptr(desc), cap, C.byref(n)))
-        self.kps, self.desc = kps[:n.value], desc[:n.value]
+        _check(lib().clb_detect_describe(self._h, _ptr(img), w, h, img.strides[0], _ptr(self._kbuf), _ptr(self._dbuf), cap, C.byref(n)))
+        # like the reference's public `kps` / `desc` members these hold the LAST frame: copy=False hands out views that the next call overwrites
+        if copy:
+            self.kps, self.desc = self._kbuf[:n.value].copy(), self._dbuf[:n.value].copy()
+        else:
+            self.kps, self.desc = self._kbuf[:n.value], self._dbuf[:n.value]
         return self.kps, self.desc
 
     def detect_and_describe_dev(self, d_img, stream=None):

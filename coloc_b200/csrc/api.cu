@@ -45,6 +45,9 @@ struct clb_detector {
     size_t level_off[CLB_MAX_LEVELS];
     LevelTex tex;        // texture views of the pyramid levels for the frame geometry tex_w x tex_h
     int tex_w, tex_h, tex_n;
+    cudaStream_t copy_stream;   // keypoint D2H of the blocking per-frame call, behind the describe kernel
+    cudaEvent_t ev_count;
+    bool copy_ready;
 };
 
 static void level_dims(const clb_detector_opts& o, int w, int h, int* ws, int* hs, float* fs) {
@@ -176,6 +179,7 @@ void clb_detector_destroy(clb_detector* d) {
     destroy_level_textures(d->tex, d->tex_n);
     d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release();
     if (d->h_total) cudaFreeHost(d->h_total);
+    if (d->copy_ready) { cudaEventDestroy(d->ev_count); cudaStreamDestroy(d->copy_stream); }
     if (d->stream) cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -236,18 +240,38 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
     LevelTable lt;
     make_table(d, w, h, lt);
     CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], gray, stride, w, h, cudaMemcpyHostToDevice, s));
-    rc = run_pipeline(d, lt, s);
+    if (!d->copy_ready) {
+        CLB_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+        CLB_CUDA(cudaEventCreateWithFlags(&d->ev_count, cudaEventDisableTiming));
+        d->copy_ready = true;
+    }
+    // the keypoints are final after the FAST stage: their count comes back while the describe kernel runs, and the keypoint
+    // D2H copy goes out on a second stream behind that kernel; only the descriptor copy follows it
+    rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
     if (rc) return rc;
-    CLB_CUDA(cudaMemcpyAsync(d->h_total, d->misc.p, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CLB_CUDA(cudaStreamSynchronize(s));
+    rc = launch_resize(lt, s);
+    if (rc) return rc;
+    int* d_total = d->misc.as<int>();
+    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    if (rc) return rc;
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaEventRecord(d->ev_count, s));
+    rc = launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex);
+    if (rc) return rc;
+    CLB_CUDA(cudaEventSynchronize(d->ev_count));
     const int n = *d->h_total;
     *n_out = n;
-    if (n > d->o.maxkp || n > cap) { snprintf(g_err, sizeof(g_err), "%d keypoints exceed capacity (cap %d, maxkp %d)", n, cap, d->o.maxkp); return CLB_ECAPACITY; }
-    if (n > 0) {
-        if (kps_out) CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, s));
-        if (desc_out) CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
-        CLB_CUDA(cudaStreamSynchronize(s));
+    if (n > d->o.maxkp || n > cap) {
+        cudaStreamSynchronize(s);
+        snprintf(g_err, sizeof(g_err), "%d keypoints exceed capacity (cap %d, maxkp %d)", n, cap, d->o.maxkp);
+        return CLB_ECAPACITY;
     }
+    if (n > 0) {
+        if (kps_out) CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, d->copy_stream));
+        if (desc_out) CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
+        if (kps_out) CLB_CUDA(cudaStreamSynchronize(d->copy_stream));
+    }
+    CLB_CUDA(cudaStreamSynchronize(s));
     return CLB_OK;
 }
 
