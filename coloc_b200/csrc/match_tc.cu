@@ -756,6 +756,14 @@ __device__ __forceinline__ void tc_mma_mxf4_ts(uint32_t d_tmem, uint32_t a_tmem,
                  ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(TC3_IDESC), "r"(accumulate), "r"(sfa), "r"(sfb) : "memory");
 }
 
+// same instruction with N = 64 (half an accumulator: DB rows 0-63 or 64-127 of the tile)
+__device__ __forceinline__ void tc_mma_mxf4_ts_n64(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t accumulate, uint32_t sfa, uint32_t sfb) {
+    constexpr uint32_t idesc = (1u << 7) | (1u << 10) | ((uint32_t)(64 >> 3) << 17) | (1u << 23) | ((uint32_t)(TC_TILE >> 4) << 24);
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], [%1], %2, %3, [%5], [%6], p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb) : "memory");
+}
+
 template <bool MASKED>
 __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcState& st) {
     float v0[32], v1[32];
@@ -792,9 +800,11 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     const uint32_t sB = (raw + 1023u) & ~1023u;
     const uint32_t sBar = sB + TC4_SMEM_B;
     const uint32_t bar_full = sBar, bar_empty = sBar + 8 * TC4_STAGES, bar_a = sBar + 16 * TC4_STAGES;
-    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 16, tmem_slot = bar_tempty + 16;
+    const uint32_t bar_tfull = bar_a + 8, bar_tempty = bar_tfull + 32, tmem_slot = bar_tempty + 32;   // [query tile][column half]
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
     uint2* smem_res = reinterpret_cast<uint2*>(tc_smem_raw + (sB - raw));      // ring reused after the sweep
+    // split: each accumulator is handed over in two 64-column halves with their own barriers (four half-accumulators rotate)
+    const bool split = dbg == 21;                              // experiment (match_tc_dbg = 21): N = 64 MMAs cost ~44 cycles instead of 32, 1 426 vs 1 148 cycles per tile
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     long long dbg_c0 = 0; unsigned long long dbg_t0 = 0;
@@ -803,7 +813,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     if (tid == 0) {
         for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, TC_QTILES); }
         tc_mbar_init(bar_a, TC4_EPI_WARPS);
-        for (int b = 0; b < 2; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, TC4_EPI_WARPS / 2); }
+        for (int b = 0; b < 4; ++b) { tc_mbar_init(bar_tfull + 8 * b, 1); tc_mbar_init(bar_tempty + 8 * b, split ? TC4_EPI_WARPS / 4 : TC4_EPI_WARPS / 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -878,63 +888,56 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                 __syncwarp();
                 tc_mbar_wait(bar_tfull, 0);
             }
-        } else if (dbg == 8) {      // timing experiment: where the issuing warp's time goes (clock64 around each section)
-            long long t_te = 0, t_fu = 0, t_is = 0, t_fx = 0, c0 = clock64();
-            for (int j = 0; j < ntiles; ++j) {
-                tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
-                tc_fence_after();
-                long long c1 = clock64(); t_te += c1 - c0; c0 = c1;
-#pragma unroll
-                for (int kb = 0; kb < TC3_KB; ++kb) {
-                    const int it = j * TC3_KB + kb;
-                    const int s = it % TC4_STAGES;
-                    tc_mbar_wait(bar_full + 8 * s, (uint32_t)((it / TC4_STAGES) & 1));
-                    c1 = clock64(); t_fu += c1 - c0; c0 = c1;
-                    tc_mbar_wait(bar_a, 0);                            // completed long ago: the fixed cost of a wait
-                    c1 = clock64(); t_fx += c1 - c0; c0 = c1;
-                    if (tc_elect_one()) {
-                        const uint64_t b0 = desc_hi | (uint64_t)(((sB + s * TC_KB_BYTES) & 0x3FFFFu) >> 4);
-                        const uint32_t a0 = tm_a + (uint32_t)(m * 64 + kb * 32);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)((kb | k) != 0), tm_sf, tm_sf + 32u);
-                        tc_commit(bar_empty + 8 * s);
-                        if (kb == TC3_KB - 1) tc_commit(bar_tfull + 8 * m);
-                    }
-                    __syncwarp();
-                    c1 = clock64(); t_is += c1 - c0; c0 = c1;
-                }
-            }
-            if (lane == 0 && qblock == 0 && tile0 == 0)
-                printf("tc4 mma warp %d: per tile  wait tempty %.1f  wait full %.1f  ready-barrier wait %.1f  issue %.1f cycles\n", m, (double)t_te / ntiles, (double)t_fu / ntiles, (double)t_fx / ntiles, (double)t_is / ntiles);
         } else {
         // The issuing thread is blocked while its MMAs execute and nothing is queued behind them, so every instruction
         // between two MMAs is tensor-pipe idle time: the operand barriers are checked BEFORE the accumulator hand-off wait
-        // (which has to be sat out anyway) and the tile's 8 MMAs then go out back to back.
+        // (which has to be sat out anyway) and the MMAs of a hand-off unit then go out back to back.
+        const uint32_t a0 = tm_a + (uint32_t)(m * 64);
         for (int j = 0; j < ntiles; ++j) {
             const int it0 = j * TC3_KB, s0 = it0 % TC4_STAGES, s1 = (it0 + 1) % TC4_STAGES;
             tc_mbar_wait(bar_full + 8 * s0, (uint32_t)((it0 / TC4_STAGES) & 1));
             tc_mbar_wait(bar_full + 8 * s1, (uint32_t)(((it0 + 1) / TC4_STAGES) & 1));
             const uint64_t b0 = desc_hi | (uint64_t)(((sB + s0 * TC_KB_BYTES) & 0x3FFFFu) >> 4);
             const uint64_t b1 = desc_hi | (uint64_t)(((sB + s1 * TC_KB_BYTES) & 0x3FFFFu) >> 4);
-            const uint32_t a0 = tm_a + (uint32_t)(m * 64);
-            if (dbg == 20) tc_mbar_spin(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
-            else           tc_mbar_wait(bar_tempty + 8 * m, (uint32_t)((j & 1) ^ 1));
-            tc_fence_after();
-            if (tc_elect_one()) {
-                if (dbg != 3) {
+            if (!split) {
+                tc_mbar_wait(bar_tempty + 16 * m, (uint32_t)((j & 1) ^ 1));
+                tc_fence_after();
+                if (tc_elect_one()) {
+                    if (dbg != 3) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
+                        for (int k = 0; k < 4; ++k)
+                            tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        tc_mma_mxf4_ts(d0, a0 + (uint32_t)(32 + k * 8), b1 + (uint64_t)(k * 2), 1u, tm_sf, tm_sf + 32u);
+                        for (int k = 0; k < 4; ++k)
+                            tc_mma_mxf4_ts(d0, a0 + (uint32_t)(32 + k * 8), b1 + (uint64_t)(k * 2), 1u, tm_sf, tm_sf + 32u);
+                    }
+                    tc_commit(bar_tfull + 16 * m);
+                    tc_commit(bar_empty + 8 * s0);
+                    tc_commit(bar_empty + 8 * s1);
                 }
-                tc_commit(bar_tfull + 8 * m);
-                tc_commit(bar_empty + 8 * s0);
-                tc_commit(bar_empty + 8 * s1);
+                __syncwarp();
+            } else {
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {         // DB rows 0-63 / 64-127 of the tile = accumulator columns 0-63 / 64-127
+                    tc_mbar_wait(bar_tempty + 16 * m + 8 * hf, (uint32_t)((j & 1) ^ 1));
+                    tc_fence_after();
+                    if (tc_elect_one()) {
+                        const uint64_t r0 = b0 + (uint64_t)(hf * 512), r1 = b1 + (uint64_t)(hf * 512);   // 64 rows x 128 B = 8 KB further
+                        const uint32_t dh = d0 + (uint32_t)(hf * 64);
+                        if (dbg != 3) {
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                tc_mma_mxf4_ts_n64(dh, a0 + (uint32_t)(k * 8), r0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)
+                                tc_mma_mxf4_ts_n64(dh, a0 + (uint32_t)(32 + k * 8), r1 + (uint64_t)(k * 2), 1u, tm_sf, tm_sf + 32u);
+                        }
+                        tc_commit(bar_tfull + 16 * m + 8 * hf);
+                        if (hf == 1) { tc_commit(bar_empty + 8 * s0); tc_commit(bar_empty + 8 * s1); }
+                    }
+                    __syncwarp();
+                }
             }
-            __syncwarp();
         }
         }
     } else {
@@ -966,6 +969,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             if (lane == 0) tc_mbar_arrive(bar_a);
         }
         const uint32_t tbase = lane_base + (uint32_t)(m * TC_TILE + half * 64);
+        const uint32_t hb = (uint32_t)(16 * m + (split ? 8 * half : 0));      // this warp's hand-off barriers
         TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
         if (dbg == 15 || dbg == 16) {      // timing experiment: bare TMEM read stream (16: only query tile 0's warps)
             float acc = 0.f;
@@ -980,12 +984,12 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             if (acc == 12345.678f) st.best = 0u;
         }
         for (int j = 0; j < (dbg >= 10 && dbg != 20 ? 0 : ntiles); ++j) {
-            if (dbg == 20) tc_mbar_spin(bar_tfull + 8 * m, (uint32_t)(j & 1));
-            else           tc_mbar_wait(bar_tfull + 8 * m, (uint32_t)(j & 1));
+            if (dbg == 20) tc_mbar_spin(bar_tfull + hb, (uint32_t)(j & 1));
+            else           tc_mbar_wait(bar_tfull + hb, (uint32_t)(j & 1));
             tc_fence_after();
             if (dbg == 1) {
                 tc_fence_before(); __syncwarp();
-                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                if (lane == 0) tc_mbar_arrive(bar_tempty + hb);
                 continue;
             }
             if (dbg == 2) {
@@ -993,7 +997,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                 tc_ld32(tbase, v0); tc_ld32(tbase + 32, v1);
                 tc_wait_ld();
                 tc_fence_before(); __syncwarp();
-                if (lane == 0) tc_mbar_arrive(bar_tempty + 8 * m);
+                if (lane == 0) tc_mbar_arrive(bar_tempty + hb);
                 float acc = 0.f;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc += v0[i] + v1[i];
@@ -1002,8 +1006,8 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             }
             const int valid = chunk_rows - j * TC_TILE - half * 64;       // rows of this half that exist
             const uint32_t row0 = (uint32_t)(j * TC_TILE + half * 64);
-            if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + 8 * m, lane, st);
-            else             tc_epilogue_half_tile<true>(tbase, row0, valid, bar_tempty + 8 * m, lane, st);
+            if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + hb, lane, st);
+            else             tc_epilogue_half_tile<true>(tbase, row0, valid, bar_tempty + hb, lane, st);
         }
         // merge the two column halves of each query by packed key.  The staging array aliases ring stage 0, which the
         // last tile's MMAs of the OTHER query tile may still be reading: wait until every epilogue warp has seen its last tile.
