@@ -893,6 +893,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         // between two MMAs is tensor-pipe idle time: the operand barriers are checked BEFORE the accumulator hand-off wait
         // (which has to be sat out anyway) and the MMAs of a hand-off unit then go out back to back.
         const uint32_t a0 = tm_a + (uint32_t)(m * 64);
+        const bool no_mma = dbg == 3;
         for (int j = 0; j < ntiles; ++j) {
             const int it0 = j * TC3_KB, s0 = it0 % TC4_STAGES, s1 = (it0 + 1) % TC4_STAGES;
             tc_mbar_wait(bar_full + 8 * s0, (uint32_t)((it0 / TC4_STAGES) & 1));
@@ -903,7 +904,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                 tc_mbar_wait(bar_tempty + 16 * m, (uint32_t)((j & 1) ^ 1));
                 tc_fence_after();
                 if (tc_elect_one()) {
-                    if (dbg != 3) {
+                    if (!no_mma) {
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             tc_mma_mxf4_ts(d0, a0 + (uint32_t)(k * 8), b0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
@@ -924,7 +925,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                     if (tc_elect_one()) {
                         const uint64_t r0 = b0 + (uint64_t)(hf * 512), r1 = b1 + (uint64_t)(hf * 512);   // 64 rows x 128 B = 8 KB further
                         const uint32_t dh = d0 + (uint32_t)(hf * 64);
-                        if (dbg != 3) {
+                        if (!no_mma) {
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
                                 tc_mma_mxf4_ts_n64(dh, a0 + (uint32_t)(k * 8), r0 + (uint64_t)(k * 2), (uint32_t)(k != 0), tm_sf, tm_sf + 32u);
