@@ -164,13 +164,6 @@ int clb_fmap_desc_dev(const clb_fmap* f, uint32_t idx, const uint64_t** d_desc_o
 // ---- batched pair matching --------------------------------------------------------------------
 namespace {
 
-struct PairPlan {
-    std::vector<int> nQ, nT;
-    std::vector<long long> out_off;
-    long long total_rows = 0;
-    int max_nQ = 0;
-};
-
 // gather of landmark rows: 4 threads per 64-byte row
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const uint4* const* __restrict__ bases, const int2* __restrict__ list, int n, uint4* __restrict__ out) {
@@ -182,33 +175,80 @@ gather_rows_kernel(const uint4* const* __restrict__ bases, const int2* __restric
 
 }  // namespace
 
-static int run_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
-                     int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
-    const int tpc = [&] {
-        std::vector<int> nQ(npairs), nT(npairs);
-        for (int p = 0; p < npairs; ++p) {
-            const FSet* q = find_set(f, pairs[p].query_idx);
-            const FSet* t = find_set(f, pairs[p].train_idx);
-            const int hi = pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi;
-            nQ[p] = hi - pairs[p].q_lo; nT[p] = t->n;
-        }
-        return tc_plan_pairs(nQ.data(), nT.data(), npairs, m->sm_count);
-    }();
-    // count the CTAs and the partial rows
-    size_t njobs = 0, part_rows = 0;
+namespace clb { int g_match_balance = -1, g_last_match_balanced = 0; }
+// g_match_balance: clb_set_param "match_balance": -1 choose by the time model, 0 uniform chunks, 1 balanced jobs
+
+// One sweep launch + one merge launch over a list of (query rows, expanded training set) views.
+// Two job layouts, chosen by the CTA time model (tc_cta_cost_us):
+//   uniform   every view cut into chunks of one common length (tc_plan_pairs): CTA = (view, 256-query block, chunk)
+//   balanced  the (view, query block) strips laid end to end and cut into one contiguous range per SM (stream-K style): a strip
+//             that straddles a range border becomes two jobs, so an SM runs ~1.5 jobs of the same total length instead of
+//             whole waves of equal CTAs -- what mid-sized problems (one 20 k x 20 k frame pair) need to fill 148 SMs.
+// Jobs are sorted longest first (blockIdx.x order = LPT packing).
+int run_views(clb_matcher* m, const clb::PairView* v, int nv, int threshold, float ratio,
+              int32_t* d_match, int32_t* d_best, int32_t* d_second, clb_partial* d_part_out, long long t_base, cudaStream_t s) {
+    const int sm = m->sm_count > 0 ? m->sm_count : 148;
+    std::vector<int> nQ(nv), nT(nv);
+    long long units = 0, strips = 0;
     int max_nQ = 0;
-    for (int p = 0; p < npairs; ++p) {
-        const FSet* q = find_set(f, pairs[p].query_idx);
-        const FSet* t = find_set(f, pairs[p].train_idx);
-        const int nQ = (pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi) - pairs[p].q_lo;
-        if (nQ > max_nQ) max_nQ = nQ;
-        if (nQ <= 0 || t->n <= 0) continue;
-        const int tiles = (t->n + 127) / 128, chunks = (tiles + tpc - 1) / tpc;
-        njobs += (size_t)((nQ + 255) / 256) * chunks;
-        part_rows += (size_t)chunks * nQ;
+    for (int p = 0; p < nv; ++p) {
+        nQ[p] = v[p].nQ > 0 ? v[p].nQ : 0; nT[p] = v[p].nT;
+        if (nQ[p] > max_nQ) max_nQ = nQ[p];
+        if (nQ[p] <= 0 || nT[p] <= 0) continue;
+        const long long qb = (nQ[p] + 255) / 256, tiles = (nT[p] + 127) / 128;
+        strips += qb; units += qb * tiles;
+    }
+    double t_uniform = 0.0;
+    const int tpc = tc_plan_pairs(nQ.data(), nT.data(), nv, sm, &t_uniform);
+    // balanced layout: one range per SM (more when a range would exceed the 2^22 rows a packed key can index)
+    long long parts = sm;
+    const double t_balanced = tc_balanced_cost_us(units, strips, sm, &parts);
+    const double quota = units > 0 ? (double)units / (double)parts : 1.0;
+    bool balanced = units >= 4 * parts && t_balanced < 0.97 * t_uniform;
+    if (g_match_balance == 0) balanced = false;
+    if (g_match_balance == 1 && units > 0) balanced = true;
+    constexpr int MINP = 4;             // no piece shorter than this many tiles (cuts snap to the strip ends)
+
+    // pass 1: count jobs / partial rows / piece-table entries; pass 2 fills the tables
+    struct Cut { int tile0, ntiles; };
+    auto cut_strip = [&](long long u0, int tiles, std::vector<Cut>& out) {
+        out.clear();
+        int t0 = 0;
+        if (balanced) {
+            // cut points = multiples of quota inside (u0, u0 + tiles)
+            long long k = (long long)((double)u0 / quota) + 1;
+            for (;; ++k) {
+                const long long cut = (long long)((double)k * quota + 0.5) - u0;
+                if (cut >= tiles) break;
+                if (cut - t0 < MINP || tiles - cut < MINP) continue;
+                out.push_back(Cut{t0, (int)(cut - t0)});
+                t0 = (int)cut;
+            }
+            out.push_back(Cut{t0, tiles - t0});
+        } else {
+            for (; t0 < tiles; t0 += tpc) out.push_back(Cut{t0, tiles - t0 < tpc ? tiles - t0 : tpc});
+        }
+    };
+    std::vector<Cut> cuts;
+    size_t njobs = 0, part_rows = 0, tab_ints = 0;
+    std::vector<int> maxp(nv, 0);
+    {
+        long long u = 0;
+        for (int p = 0; p < nv; ++p) {
+            if (nQ[p] <= 0 || nT[p] <= 0) continue;
+            const int qb = (nQ[p] + 255) / 256, tiles = (nT[p] + 127) / 128;
+            for (int b = 0; b < qb; ++b, u += tiles) {
+                cut_strip(u, tiles, cuts);
+                njobs += cuts.size();
+                if ((int)cuts.size() > maxp[p]) maxp[p] = (int)cuts.size();
+            }
+            part_rows += (size_t)maxp[p] * nQ[p];
+            if (balanced) tab_ints += (size_t)qb * (1 + maxp[p]);
+        }
     }
     if (njobs > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "pair list too large for one launch"); return CLB_EINVAL; }
-    const size_t tab_bytes = njobs * sizeof(TcJob) + (size_t)npairs * sizeof(MergeJob);
+    const size_t jobs_bytes = njobs * sizeof(TcJob), merge_bytes = (size_t)nv * sizeof(MergeJob);
+    const size_t tab_bytes = jobs_bytes + merge_bytes + tab_ints * sizeof(int);
     // the previous call's table copy must have left the pinned staging area before it is rewritten
     if (m->jobs_ev_set) CLB_CUDA(cudaEventSynchronize(m->jobs_ev));
     int rc = pinned_reserve(&m->jobs_host, &m->jobs_host_cap, tab_bytes);
@@ -217,36 +257,45 @@ static int run_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npa
     CLB_CUDA(m->pair_part.reserve((part_rows > 0 ? part_rows : 1) * sizeof(uint2)));
     TcJob* tj = reinterpret_cast<TcJob*>(m->jobs_host);
     MergeJob* mj = reinterpret_cast<MergeJob*>(tj + njobs);
+    int* tab = reinterpret_cast<int*>(mj + nv);
+    const int* d_tab = reinterpret_cast<const int*>(static_cast<char*>(m->jobs.p) + jobs_bytes + merge_bytes);
     uint2* part = m->pair_part.as<uint2>();
-    size_t j = 0, part_off = 0;
-    long long out_off = 0;
-    for (int p = 0; p < npairs; ++p) {
-        const FSet* q = find_set(f, pairs[p].query_idx);
-        const FSet* t = find_set(f, pairs[p].train_idx);
-        const int q_lo = pairs[p].q_lo;
-        const int nQ = (pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi) - q_lo;
-        const int tiles = (t->n + 127) / 128;
-        const int chunks = (nQ > 0 && t->n > 0) ? (tiles + tpc - 1) / tpc : 0;
+    size_t j = 0, part_off = 0, tab_off = 0;
+    long long out_off = 0, u = 0;
+    for (int p = 0; p < nv; ++p) {
+        const int tiles = nT[p] > 0 ? (nT[p] + 127) / 128 : 0;
+        const int qb = nQ[p] > 0 && tiles > 0 ? (nQ[p] + 255) / 256 : 0;
         MergeJob& mg = mj[p];
         mg.partial = part + part_off;
-        mg.match = d_match + out_off;
+        mg.match = d_match ? d_match + out_off : nullptr;
         mg.best = d_best ? d_best + out_off : nullptr;
         mg.second = d_second ? d_second + out_off : nullptr;
-        mg.nQ = nQ > 0 ? nQ : 0; mg.nT = t->n; mg.nchunks = chunks; mg.rows_per_chunk = tpc * 128;
-        for (int c = 0; c < chunks; ++c) {
-            const int tile0 = c * tpc, ntiles = std::min(tpc, tiles - tile0);
-            for (int b = 0; b < (nQ + 255) / 256; ++b) {
+        mg.part_out = d_part_out ? d_part_out + out_off : nullptr;
+        mg.t_base = t_base;
+        mg.nQ = nQ[p]; mg.nT = nT[p]; mg.nchunks = qb > 0 ? maxp[p] : 0; mg.rows_per_chunk = tpc * 128; mg.maxp = maxp[p]; mg._pad = 0;
+        mg.pieces = nullptr; mg.base_rows = nullptr;
+        int* np_tab = nullptr; int* base_tab = nullptr;
+        if (balanced && qb > 0) {
+            np_tab = tab + tab_off; base_tab = np_tab + qb;
+            mg.pieces = d_tab + tab_off; mg.base_rows = mg.pieces + qb;
+            tab_off += (size_t)qb * (1 + maxp[p]);
+        }
+        for (int b = 0; b < qb; ++b, u += tiles) {
+            cut_strip(u, tiles, cuts);
+            if (np_tab) np_tab[b] = (int)cuts.size();
+            for (size_t c = 0; c < cuts.size(); ++c) {
+                if (base_tab) base_tab[(size_t)b * maxp[p] + c] = cuts[c].tile0 * 128;
                 TcJob& job = tj[j++];
-                job.Q = reinterpret_cast<const uint32_t*>(q->desc.as<uint64_t>() + 8ll * q_lo);
-                job.Tx = t->tx.as<uint8_t>();
-                job.partial_chunk = part + part_off + (size_t)c * nQ;
-                job.nQ = nQ; job.qblock = b; job.tile0 = tile0; job.ntiles = ntiles;
-                job.chunk_rows = std::min(ntiles * 128, t->n - tile0 * 128);
+                job.Q = reinterpret_cast<const uint32_t*>(v[p].Q);
+                job.Tx = v[p].Tx;
+                job.partial_chunk = part + part_off + c * (size_t)nQ[p];
+                job.nQ = nQ[p]; job.qblock = b; job.tile0 = cuts[c].tile0; job.ntiles = cuts[c].ntiles;
+                job.chunk_rows = std::min(cuts[c].ntiles * 128, nT[p] - cuts[c].tile0 * 128);
                 job._pad = 0;
             }
         }
-        part_off += (size_t)chunks * (nQ > 0 ? nQ : 0);
-        out_off += nQ > 0 ? nQ : 0;
+        part_off += (size_t)maxp[p] * nQ[p];
+        out_off += nQ[p];
     }
     // longest CTAs first: the hardware hands out blockIdx.x in order, so this is longest-processing-time-first packing
     std::stable_sort(tj, tj + njobs, [](const TcJob& a, const TcJob& b) { return a.ntiles > b.ntiles; });
@@ -258,7 +307,23 @@ static int run_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npa
     rc = launch_match_tc_jobs(m->jobs.as<TcJob>(), (int)njobs, s);
     if (rc) return rc;
     g_last_match_path = 4;
-    return launch_merge_jobs(reinterpret_cast<const MergeJob*>(m->jobs.as<TcJob>() + njobs), npairs, max_nQ, threshold, ratio, s);
+    g_last_match_balanced = balanced ? 1 : 0;
+    return launch_merge_jobs(reinterpret_cast<const MergeJob*>(m->jobs.as<TcJob>() + njobs), nv, max_nQ, threshold, ratio, s);
+}
+
+static int run_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, int threshold, float ratio,
+                     int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
+    std::vector<PairView> views((size_t)npairs);
+    for (int p = 0; p < npairs; ++p) {
+        const FSet* q = find_set(f, pairs[p].query_idx);
+        const FSet* t = find_set(f, pairs[p].train_idx);
+        const int hi = pairs[p].q_hi < 0 ? q->n : pairs[p].q_hi;
+        views[p].Q = q->desc.as<uint64_t>() + 8ll * pairs[p].q_lo;
+        views[p].nQ = hi - pairs[p].q_lo;
+        views[p].Tx = t->tx.as<uint8_t>();
+        views[p].nT = t->n;
+    }
+    return run_views(m, views.data(), npairs, threshold, ratio, d_match, d_best, d_second, nullptr, 0, s);
 }
 
 static int check_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npairs, long long* total_rows) {

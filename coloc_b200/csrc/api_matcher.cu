@@ -9,6 +9,28 @@ using namespace clb;
 
 #include "matcher_priv.cuh"
 
+// One (Q, T) problem: the tensor-core sweep goes through the job-list machinery (api_fmap.cu) when its balanced layout is
+// modelled faster than whole waves of equal CTAs (mid-sized problems); everything else through launch_match.
+static int match_dispatch(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t t_base,
+                          int threshold, float ratio, int32_t* d_match, int32_t* d_best, int32_t* d_second,
+                          clb_partial* d_partial, cudaStream_t s, const void* Qx, const void* Tx) {
+    if (Tx && nT > 0 && nQ > 0 && tc_version() == 4 && g_match_balance != 0) {
+        const int sm = m->sm_count > 0 ? m->sm_count : 148;
+        const long long qb = (nQ + 255) / 256, tiles = (nT + 127) / 128, units = qb * tiles;
+        double t_uniform = 0.0;
+        tc_plan_pairs(&nQ, &nT, 1, sm, &t_uniform);
+        long long parts = sm;
+        const double t_bal = tc_balanced_cost_us(units, qb, sm, &parts);
+        if (g_match_balance == 1 || (units >= 4 * parts && t_bal < 0.97 * t_uniform)) {
+            clb::PairView v; v.Q = dQ; v.nQ = nQ; v.Tx = static_cast<const uint8_t*>(Tx); v.nT = nT;
+            return run_views(m, &v, 1, threshold, ratio, d_match, d_best, d_second, d_partial, t_base, s);
+        }
+    }
+    g_last_match_balanced = 0;
+    return launch_match(dQ, nQ, dT, nT, t_base, m->scratch.p, m->scratch.cap, m->sm_count, threshold, ratio,
+                        d_match, d_best, d_second, d_partial, s, Qx, Tx);
+}
+
 // Expand the operands when the tensor-core path applies; *Qx / *Tx stay NULL for the POPC path.
 // `map` = T is the resident map (expanded once per clb_set_map, not per query set).
 static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, bool map, cudaStream_t s,
@@ -56,7 +78,7 @@ static int run_host(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* 
     rc = prepare_tc(m, dQ, nQ, dT, nT, map, s, &Qx, &Tx);
     if (rc) return rc;
     int32_t* o = m->out.as<int32_t>();
-    rc = launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, ratio,
+    rc = match_dispatch(m, dQ, nQ, dT, nT, 0, threshold, ratio,
                       o, best_out ? o + nQ : nullptr, second_out ? o + 2 * (size_t)nQ : nullptr, nullptr, s, Qx, Tx);
     if (rc) return rc;
     if (match_out) CLB_CUDA(cudaMemcpyAsync(match_out, o, (size_t)nQ * 4, cudaMemcpyDeviceToHost, s));
@@ -125,8 +147,7 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
             if (rc) return rc;
             Tx = m->sx[b].p;
         }
-        rc = launch_match(dQ, nQ, m->sraw[b].as<uint64_t>(), rows, t_base + start, m->scratch.p, m->scratch.cap, m->sm_count,
-                          0, 0.f, nullptr, nullptr, nullptr, parts + (size_t)k * nQ, s, Qx, Tx);
+        rc = match_dispatch(m, dQ, nQ, m->sraw[b].as<uint64_t>(), rows, t_base + start, 0, 0.f, nullptr, nullptr, nullptr, parts + (size_t)k * nQ, s, Qx, Tx);
         if (rc) return rc;
         CLB_CUDA(cudaEventRecord(m->ev_rawfree[b], s));
         start += sz;
@@ -235,7 +256,7 @@ int clb_match_2nn_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
     const void *Qx, *Tx;
     rc = prepare_tc(m, dQ, nQ, dT, nT, false, s, &Qx, &Tx);
     if (rc) return rc;
-    return launch_match(dQ, nQ, dT, nT, 0, m->scratch.p, m->scratch.cap, m->sm_count, threshold, 0.f,
+    return match_dispatch(m, dQ, nQ, dT, nT, 0, threshold, 0.f,
                         d_match_out, d_best_out, d_second_out, nullptr, s, Qx, Tx);
 }
 
@@ -283,8 +304,7 @@ int clb_match_map_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int threshold,
     const void *Qx, *Tx;
     rc = prepare_tc(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, true, s, &Qx, &Tx);
     if (rc) return rc;
-    return launch_match(dQ, nQ, m->map.as<uint64_t>(), m->n_map, 0, m->scratch.p, m->scratch.cap, m->sm_count,
-                        threshold < 0 ? m->o.thresh : threshold, 0.f, d_match_out, d_best_out, d_second_out, nullptr, s, Qx, Tx);
+    return match_dispatch(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, 0, threshold < 0 ? m->o.thresh : threshold, 0.f, d_match_out, d_best_out, d_second_out, nullptr, s, Qx, Tx);
 }
 
 int clb_match_map_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int64_t t_base,
@@ -298,7 +318,7 @@ int clb_match_map_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, int64_
     const void *Qx, *Tx;
     rc = prepare_tc(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, true, s, &Qx, &Tx);
     if (rc) return rc;
-    return launch_match(dQ, nQ, m->map.as<uint64_t>(), m->n_map, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
+    return match_dispatch(m, dQ, nQ, m->map.as<uint64_t>(), m->n_map, t_base, 0, 0.f,
                         nullptr, nullptr, nullptr, d_partial_out, s, Qx, Tx);
 }
 
@@ -315,7 +335,7 @@ int clb_match_partial_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint
     const void *Qx, *Tx;
     rc = prepare_tc(m, dQ, nQ, dT, nT, false, s, &Qx, &Tx);
     if (rc) return rc;
-    return launch_match(dQ, nQ, dT, nT, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
+    return match_dispatch(m, dQ, nQ, dT, nT, t_base, 0, 0.f,
                         nullptr, nullptr, nullptr, d_partial_out, s, Qx, Tx);
 }
 
@@ -330,8 +350,8 @@ int clb_match_partial_hostdb(clb_matcher* m, const uint64_t* dQ, int nQ, const u
     if (nT == 0) {
         rc = ensure(m, nQ, 0);
         if (rc) return rc;
-        return launch_match(dQ, nQ, nullptr, 0, t_base, m->scratch.p, m->scratch.cap, m->sm_count, 0, 0.f,
-                            nullptr, nullptr, nullptr, d_partial_out, s);
+        return match_dispatch(m, dQ, nQ, nullptr, 0, t_base, 0, 0.f,
+                              nullptr, nullptr, nullptr, d_partial_out, s, nullptr, nullptr);
     }
     return match_partial_streamed(m, dQ, nQ, T_host, nT, t_base, d_partial_out, s);
 }

@@ -115,13 +115,21 @@ struct TcJob {
     int nQ, qblock, tile0, ntiles, chunk_rows, _pad;
 };
 struct MergeJob {
-    const uint2* partial;
-    int32_t *match, *best, *second;   // best / second may be NULL
-    int nQ, nT, nchunks, rows_per_chunk;
+    const uint2* partial;             // [piece slot][nQ]
+    int32_t *match, *best, *second;   // any may be NULL
+    clb_partial* part_out;            // optional per-query partial (row indices + t_base)
+    long long t_base;
+    // uniform chunks: `nchunks` pieces of `rows_per_chunk` rows for every query (pieces == NULL); balanced jobs: query block b
+    // (256 queries) has pieces[b] pieces, piece k starting at DB row base_rows[b * maxp + k]
+    const int* pieces;
+    const int* base_rows;
+    int nQ, nT, nchunks, rows_per_chunk, maxp, _pad;
 };
 size_t tc4_t_bytes(int nT);
+double tc_cta_cost_us(int tiles);
+double tc_balanced_cost_us(long long units, long long strips, int sm_count, long long* parts_out);   // modelled time of the balanced job layout
 int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s);
-int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count);      // -> DB tiles per chunk, shared by all pairs
+int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count, double* t_us_out = nullptr);   // -> DB tiles per chunk, shared by all pairs (+ modelled time)
 int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s);
 int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int threshold, float ratio, cudaStream_t s);
 // pyramid.cu

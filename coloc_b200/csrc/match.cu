@@ -356,23 +356,33 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
     return CLB_OK;
 }
 
-// batched merge_chunks_kernel: blockIdx.y = pair of the list
+// batched merge_chunks_kernel: blockIdx.y = pair of the list; pieces are uniform chunks or the per-query-block pieces of a
+// balanced job list
 __global__ void __launch_bounds__(256)
 merge_jobs_kernel(const MergeJob* __restrict__ jobs, int threshold, float ratio) {
     const MergeJob j = jobs[blockIdx.y];
     const int qi = blockIdx.x * blockDim.x + threadIdx.x;
     if (qi >= j.nQ) return;
+    const int qb = qi >> 8;
+    const int np = j.pieces ? j.pieces[qb] : j.nchunks;
     int best = CLB_BEST_NONE, second = CLB_SECOND_NONE, best_i = -1;
-    for (int c = 0; c < j.nchunks; ++c) {
+    for (int c = 0; c < np; ++c) {
         const uint2 p = j.partial[(size_t)c * j.nQ + qi];
         if (p.x == 0xFFFFFFFFu) continue;
-        feed((int)(p.x >> MT_KEY_SHIFT), c * j.rows_per_chunk + (int)(p.x & MT_IDX_MASK), best, best_i, second);
+        const int base = j.pieces ? j.base_rows[qb * j.maxp + c] : c * j.rows_per_chunk;
+        feed((int)(p.x >> MT_KEY_SHIFT), base + (int)(p.x & MT_IDX_MASK), best, best_i, second);
         feed(p.y == 0xFFFFFFFFu ? CLB_BEST_NONE : (int)(p.y >> MT_KEY_SHIFT), -1, best, best_i, second);
     }
-    bool ok;
-    if (ratio > 0.f) ok = j.nT >= 2 && (float)best < ratio * (float)second;
-    else             ok = j.nT > 0 && (second - best > threshold);
-    j.match[qi] = ok ? best_i : CLB_NO_MATCH;
+    if (j.part_out) {
+        clb_partial o; o.best_d = best; o.best_i = best_i < 0 ? -1 : (int32_t)(j.t_base + best_i); o.second_d = second; o._pad = 0;
+        j.part_out[qi] = o;
+    }
+    if (j.match) {
+        bool ok;
+        if (ratio > 0.f) ok = j.nT >= 2 && (float)best < ratio * (float)second;
+        else             ok = j.nT > 0 && (second - best > threshold);
+        j.match[qi] = ok ? best_i : CLB_NO_MATCH;
+    }
     if (j.best) j.best[qi] = best;
     if (j.second) j.second[qi] = second;
 }

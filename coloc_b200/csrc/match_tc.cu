@@ -1080,6 +1080,13 @@ int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, 
     return CLB_OK;
 }
 
+// CTA time model (us) fitted to tools/tc_small.py sweeps: ~28 us of prologue (TMEM allocation, query expansion, barriers), 0.60 us
+// per DB tile in steady state, and 0.16 us more per tile over the first ~200 tiles while the per-query thresholds are still open
+// and most 16-column groups take the update path (54 tiles: 69 us, 161: 150 us, 5 208: 3.3 ms)
+double tc_cta_cost_us(int tiles) {
+    return 28.0 + 0.60 * (double)tiles + 0.157 * (double)(tiles < 200 ? tiles : 200);
+}
+
 // choose the DB chunk count: fewest chunks whose CTA count fills whole waves of `sm_count` SMs
 void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, int* tpc_out) {
     const int qblocks = (nQ + TC_QROWS - 1) / TC_QROWS;
@@ -1094,15 +1101,14 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
         best_c = g_match_tc_chunks < max_chunks ? g_match_tc_chunks : max_chunks;
         if (best_c < min_chunks) best_c = min_chunks;
     } else {
-        // time model (tools/tc_small.py): a CTA costs ~0.62 us per DB tile plus ~15 us of prologue and epilogue warm-up
-        // (every query's threshold starts open), and the busiest SM runs `waves` CTAs back to back
+        // the busiest SM runs `waves` CTAs of tc_cta_cost_us(tpc) back to back
         double best_t = 1e30;
         for (int c = best_c; c <= max_chunks; ++c) {
             const int tpc = (total_tiles + c - 1) / c;
             const int real_c = (total_tiles + tpc - 1) / tpc;
             const long long ctas = (long long)qblocks * real_c;
             const long long waves = (ctas + sm_count - 1) / sm_count;
-            const double t = (double)waves * (0.62 * tpc + 15.0);
+            const double t = (double)waves * tc_cta_cost_us(tpc);
             if (t < best_t * 0.98) { best_t = t; best_c = c; }
         }
     }
@@ -1131,7 +1137,7 @@ int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s) {
 
 // One chunk length (in DB tiles) for every pair of the list, chosen with the same CTA cost model as tc_plan: the
 // CTA count is summed over the pairs, so small pairs fill each other's waves.
-int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count) {
+int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count, double* t_us_out) {
     int max_tiles = 1;
     for (int p = 0; p < npairs; ++p) {
         const int t = (nT[p] + TC_TILE - 1) / TC_TILE;
@@ -1150,10 +1156,23 @@ int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count) {
             ctas += (long long)((nQ[p] + TC_QROWS - 1) / TC_QROWS) * ((tiles + tpc - 1) / tpc);
         }
         const long long waves = (ctas + sm_count - 1) / sm_count;
-        const double t = (double)waves * (0.62 * tpc + 15.0);
+        const double t = (double)waves * tc_cta_cost_us(tpc);
         if (t < best_t * 0.98) { best_t = t; best_tpc = tpc; }
     }
+    if (t_us_out) *t_us_out = best_t;
     return best_tpc > 0 ? best_tpc : 1;
+}
+
+// balanced layout: `units` DB tiles in `strips` (view, query block) strips, cut into one contiguous range per SM (more when a range
+// would exceed what a packed key can index); an SM then runs its range as 1 + (strips that straddle a border) jobs
+double tc_balanced_cost_us(long long units, long long strips, int sm_count, long long* parts_out) {
+    long long parts = sm_count;
+    while (units / parts > 30000) parts += sm_count;
+    if (parts_out) *parts_out = parts;
+    if (units <= 0) return 0.0;
+    const long long quota = (units + parts - 1) / parts;
+    const double extra_jobs = (double)(strips < parts ? strips : parts) / (double)parts;
+    return 1.03 * (tc_cta_cost_us((int)quota) + 28.0 * extra_jobs);
 }
 
 int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s) {

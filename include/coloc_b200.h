@@ -287,7 +287,9 @@ int  clb_set_timing(int on);
 /* tuning knobs for experiments: "match_rq" (0,1,2,4), "match_hs" (0..3), "match_chunks" (0 = auto) for the
  * POPC kernel; "match_tc" (-1 auto: tensor-core path from 2^24 comparisons up, 0 never, 1 always),
  * "match_tc_ver" (1 queries in shared memory, 2 queries in TMEM), "match_tc_chunks" (0 = auto).
- * clb_get_param also answers "last_match_path": 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2. */
+ * "match_balance" (-1 the time model chooses, 0 uniform chunks, 1 balanced job list: the (query block) strips cut into one contiguous
+ * range per SM), "match_slice_rows" (first H2D slice of the streamed host-DB path).
+ * clb_get_param also answers "last_match_balanced" and "last_match_path": 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2. */
 int  clb_set_param(const char* name, int value);
 int  clb_get_param(const char* name, int* value_out);
 float clb_last_kernel_ms(const char* which);   /* "match", "describe", "fast", "resize", "merge" */

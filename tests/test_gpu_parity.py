@@ -608,3 +608,35 @@ def test_streamed_host_db_equals_oracle(clb, oracle, tc):
         m.close()
     finally:
         clb.set_param("match_tc", -1); clb.set_param("match_slice_rows", 524288)
+
+
+@pytest.mark.parametrize("nq,nt", [(300, 5000), (5000, 5000), (2049, 4100), (777, 12345), (20000, 20000), (130, 70000)])
+def test_match_balanced_jobs_vs_oracle(clb, oracle, nq, nt):
+    """balanced job layout (query-block strips cut into one range per SM, pieces of unequal length per query block) == oracle,
+    for direct calls, partial outputs with a row base, and the resident map"""
+    import torch
+    clb.set_param("match_tc", 1); clb.set_param("match_balance", 1)
+    try:
+        T = synth.random_descriptors(nt, 3 + nt); Q, _ = synth.planted_queries(T, nq, 5 + nq)
+        T[nt // 2] = T[1]; T[nt - 1] = T[1]; Q[0] = T[1]
+        ref = oracle.match_2nn(Q, T, 40)
+        m = clb.Matcher(maxkp=4096)
+        got = m.compute_matches(Q, T, 40, want_dist=True)
+        assert clb.get_param("last_match_balanced") == 1
+        assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+        dQ = torch.from_numpy(Q.view(np.int64)).cuda(); dT = torch.from_numpy(T.view(np.int64)).cuda()
+        cut = nt // 3
+        parts = torch.zeros((2, nq, 4), dtype=torch.int32, device="cuda"); out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+        m.match_partial_dev(dQ, nq, dT[:cut], cut, 0, parts[0]); m.match_partial_dev(dQ, nq, dT[cut:], nt - cut, cut, parts[1])
+        m.merge_partials_dev(parts, 2, nq, 40, out[0], out[1], out[2])
+        torch.cuda.synchronize()
+        assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
+        m.set_map_data(T)
+        got = m.match_with_map(Q, 40, want_dist=True)
+        assert all(np.array_equal(a, b) for a, b in zip(got, ref))
+        clb.set_param("match_balance", 0)
+        got = m.compute_matches(Q, T, 40, want_dist=True)
+        assert clb.get_param("last_match_balanced") == 0 and all(np.array_equal(a, b) for a, b in zip(got, ref))
+        m.close()
+    finally:
+        clb.set_param("match_tc", -1); clb.set_param("match_balance", -1)

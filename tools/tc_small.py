@@ -11,11 +11,13 @@ Q = torch.from_numpy(synth.random_descriptors(nq, 43).view(np.int64)).cuda()
 m = clb.Matcher(maxkp=nt); out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
 clb.set_timing(True)
 for ch in [int(x) for x in sys.argv[3:]]:
-    clb.set_param("match_tc_chunks", ch)
+    # chunks = -1: balanced job list; otherwise uniform chunks (0 = planner's choice)
+    clb.set_param("match_balance", 1 if ch == -1 else (-1 if ch == -2 else 0))     # -2: let the time model choose the layout
+    clb.set_param("match_tc_chunks", max(ch, 0))
     ts = []
     for _ in range(6):
         m.match_dev(Q, nq, T, nt, 40, out[0], out[1], out[2], stream=torch.cuda.current_stream().cuda_stream)
         torch.cuda.synchronize()
         ts.append((clb.last_kernel_ms("match"), clb.last_kernel_ms("expand"), clb.last_kernel_ms("merge")))
     t = np.min(np.array(ts[1:]), axis=0)
-    print(f"chunks={ch}: match {t[0]*1e3:.1f} us expand(last) {t[1]*1e3:.1f} us merge {t[2]*1e3:.1f} us -> {nq*nt/t[0]/1e9:.2f} T cmp/s", flush=True)
+    print(f"chunks={ch} (balanced={clb.get_param('last_match_balanced')}): match {t[0]*1e3:.1f} us expand(last) {t[1]*1e3:.1f} us merge {t[2]*1e3:.1f} us -> {nq*nt/t[0]/1e9:.2f} T cmp/s", flush=True)
