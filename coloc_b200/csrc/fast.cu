@@ -32,21 +32,14 @@ struct RowMap {   // global row index <-> (level, y)
     int n; int row_base[CLB_MAX_LEVELS + 1];
 };
 
-// cardinal early-out (KFAST.h:186-235): any 9-arc contains two adjacent compass points
-__device__ __forceinline__ bool fast_cardinal(const uint8_t* __restrict__ p, int stride, int t) {
-    const int c = p[0];
-    const int hi = c + t, lo = c - t;
-    const int p9 = p[3 * stride], p5 = p[3], p1 = p[-3 * stride], p13 = p[-3];
-    const bool b = ((p9 > hi) & (p5 > hi)) | ((p5 > hi) & (p1 > hi)) | ((p1 > hi) & (p13 > hi)) | ((p13 > hi) & (p9 > hi));
-    const bool d = ((p9 < lo) & (p5 < lo)) | ((p5 < lo) & (p1 < lo)) | ((p1 < lo) & (p13 < lo)) | ((p13 < lo) & (p9 < lo));
-    return b | d;
-}
-
-// corner test + score of a pixel that passed fast_cardinal
 __device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int stride, int t) {
     const int c = p[0];
     const int hi = c + t, lo = c - t;
+    // cardinal early-out (KFAST.h:186-235): any 9-arc contains two adjacent compass points
     const int p9 = p[3 * stride], p5 = p[3], p1 = p[-3 * stride], p13 = p[-3];
+    const bool b = ((p9 > hi) & (p5 > hi)) | ((p5 > hi) & (p1 > hi)) | ((p1 > hi) & (p13 > hi)) | ((p13 > hi) & (p9 > hi));
+    const bool d = ((p9 < lo) & (p5 < lo)) | ((p5 < lo) & (p1 < lo)) | ((p1 < lo) & (p13 < lo)) | ((p13 < lo) & (p9 < lo));
+    if (!(b | d)) return 0;
     int ring[16];
     ring[0] = p9;                 ring[1] = p[3 * stride + 1];  ring[2] = p[2 * stride + 2];  ring[3] = p[stride + 3];
     ring[4] = p5;                 ring[5] = p[-stride + 3];     ring[6] = p[-2 * stride + 2]; ring[7] = p[-3 * stride + 1];
@@ -93,8 +86,6 @@ fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __res
                 int do_nms, int* __restrict__ row_count) {
     __shared__ __align__(16) uint8_t px[FT_SH * FT_SSTRIDE];
     __shared__ uint8_t sc[FT_CH * FT_CSTRIDE];
-    __shared__ uint16_t cand_list[FT_CH * FT_CW];
-    __shared__ int ncand;
 
     int tile = blockIdx.x, L = 0, tx_n = 0;
     for (; L < lt.n; ++L) {
@@ -127,32 +118,14 @@ fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __res
     }
     __syncthreads();
 
-    // scores on the (TW+2) x (TH+2) region, in two passes so that the expensive part runs on dense warps: (a) every position
-    // takes the 4-pixel cardinal pre-test (~10 % pass on textured frames) and the survivors are queued in shared memory,
-    // (b) the queue is scored -- ring masks, 9-run test, sliding min/max -- one candidate per thread
-    if (tid == 0) ncand = 0;
-    __syncthreads();
-    for (int i = tid; i < ((FT_CH * FT_CW + 255) & ~255); i += 256) {
-        bool cand = false;
-        if (i < FT_CH * FT_CW) {
-            const int r = i / FT_CW, c = i % FT_CW;
-            const int gx = x0 - 1 + c, gy = y0 - 1 + r;
-            sc[r * FT_CSTRIDE + c] = 0;
-            if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3)
-                cand = fast_cardinal(&px[(r + 3) * FT_SSTRIDE + (c + 3)], FT_SSTRIDE, thresh);
-        }
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, cand);
-        int base = 0;
-        if ((tid & 31) == 0 && bal) base = atomicAdd(&ncand, __popc(bal));
-        base = __shfl_sync(0xFFFFFFFFu, base, 0);
-        if (cand) cand_list[base + __popc(bal & ((1u << (tid & 31)) - 1u))] = (uint16_t)i;
-    }
-    __syncthreads();
-    const int nc = ncand;
-    for (int k = tid; k < nc; k += 256) {
-        const int i = cand_list[k];
+    // scores on the (TW+2) x (TH+2) region
+    for (int i = tid; i < FT_CH * FT_CW; i += 256) {
         const int r = i / FT_CW, c = i % FT_CW;
-        sc[r * FT_CSTRIDE + c] = (uint8_t)fast_score_px(&px[(r + 3) * FT_SSTRIDE + (c + 3)], FT_SSTRIDE, thresh);
+        const int gx = x0 - 1 + c, gy = y0 - 1 + r;
+        int s = 0;
+        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3)
+            s = fast_score_px(&px[(r + 3) * FT_SSTRIDE + (c + 3)], FT_SSTRIDE, thresh);
+        sc[r * FT_CSTRIDE + c] = (uint8_t)s;
     }
     __syncthreads();
 
