@@ -299,23 +299,35 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
     maxkp = 400000 if w * h > 2000000 else 120000
     fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp)
     m = clb.Matcher(maxkp=maxkp) if with_match else None
-    out = torch.zeros(maxkp, dtype=torch.int32, device="cuda") if with_match else None
+    # match lists are read back one frame late (two device + two pinned host buffers): the host never waits on the sweep it
+    # has just queued, as a consumer that pipelines its geometric stage would not
+    outs = [torch.zeros(maxkp, dtype=torch.int32, device="cuda") for _ in range(2)] if with_match else None
+    houts = [torch.zeros(maxkp, dtype=torch.int32).pin_memory() for _ in range(2)] if with_match else None
+    evs = [torch.cuda.Event() for _ in range(2)] if with_match else None
     st = torch.cuda.current_stream().cuda_stream
     res = {}
 
     def run(n):
         sub = done = 0; nk = 0; ncmp = 0; nm = 0
         prev = None
+        pending = None                      # (buffer index, rows) of the match list still in flight
         while done < n:
             while sub < n and fs.in_flight() < 3:
                 fs.submit(pins[sub % distinct].numpy(), tag=sub); sub += 1
             tag, k, d, dk, dd, cnt = fs.next(copy=False)
             nk += cnt
             if with_match and prev is not None and cnt > 0 and prev[1] > 0:
-                m.match_dev(dd, cnt, prev[0], prev[1], 40, out, stream=st)
-                nm += int((out[:cnt].cpu() >= 0).sum()); ncmp += cnt * prev[1]
+                b = done & 1
+                m.match_dev(dd, cnt, prev[0], prev[1], 40, outs[b], stream=st)
+                houts[b][:cnt].copy_(outs[b][:cnt], non_blocking=True); evs[b].record()
+                ncmp += cnt * prev[1]
+                if pending is not None:
+                    evs[pending[0]].synchronize(); nm += int((houts[pending[0]][:pending[1]] >= 0).sum())
+                pending = (b, cnt)
             prev = (dd, cnt)
             done += 1
+        if pending is not None:
+            evs[pending[0]].synchronize(); nm += int((houts[pending[0]][:pending[1]] >= 0).sum())
         return nk, ncmp, nm
 
     run(min(8, nframes))
