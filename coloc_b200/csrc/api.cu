@@ -12,7 +12,7 @@ namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex, g_match_slice_rows, g_match_balance, g_last_match_balanced;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex, g_latch_var, g_match_slice_rows, g_match_balance, g_last_match_balanced;
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -123,6 +123,7 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_balance")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_balance = value; }
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
+    else if (!strcmp(name, "latch_var")) g_latch_var = value & 3;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
     else return CLB_EINVAL;
     return CLB_OK;
