@@ -576,6 +576,14 @@ def run_ours(args, rank, world, local_rank):
                          "hamming = (512 - <q,t>)/2 over +-1 E4M3 operands, tcgen05.mma kind::f8f6f4 M128 N128 K32, fp32 accumulate "
                          "(exact); 1024 flop per comparison; DB expansion (64 B -> 512 B per row) is inside the step"),
                 "pipes": pipes}
+    try:    # dram__bytes_read + dram__bytes_write of one launch of this kernel at this size (one `ncu --set full` capture, committed)
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_match_traffic.json")) as f:
+            tj = json.load(f)
+        if tj.get("kernel") == roof.get("kernel") and world == 1 and NQ == 50000 and NT == 2000000:
+            roof["traffic"] = tj["traffic_bytes_per_launch"]
+            roof["traffic_detail"] = {k: tj[k] for k in ("algorithmic_bytes_per_launch", "tensor_pipe_active_pct_of_active", "sm_clock_ghz", "source", "reading")}
+    except (OSError, ValueError, KeyError):
+        pass
     line = {"metric": "hamming_512b_comparisons_per_s", "value": value, "unit": "comparisons/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": value / PUBLISHED_CMP_S,

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
-"""short single-GPU targets for `ncu --set full` captures: `match` (50k x 100k rows), `detect` (1280x720 frames),
-`detect4k` (3840x2160)."""
+"""short single-GPU targets for `ncu --set full` captures: `match` (50k x 100k rows), `matchfull` (the bench step: 50k x 2M rows),
+`detect` (1280x720 frames), `detect4k` (3840x2160)."""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -9,8 +9,8 @@ import torch
 import coloc_b200 as clb
 from coloc_b200 import synth
 what = sys.argv[1] if len(sys.argv) > 1 else "match"
-if what == "match":
-    nq, nt = 50000, 100000
+if what in ("match", "matchfull"):
+    nq, nt = 50000, (100000 if what == "match" else 2000000)
     T = torch.from_numpy(synth.random_descriptors(nt, 42).view(np.int64)).cuda()
     Q = torch.from_numpy(synth.random_descriptors(nq, 43).view(np.int64)).cuda()
     m = clb.Matcher(maxkp=nt); out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
