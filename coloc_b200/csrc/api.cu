@@ -12,7 +12,7 @@ namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
 int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex, g_latch_var, g_match_slice_rows, g_match_balance, g_last_match_balanced;
+extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_fast_var, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex, g_latch_var, g_match_slice_rows, g_match_balance, g_last_match_balanced;
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -125,6 +125,7 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
     else if (!strcmp(name, "latch_var")) g_latch_var = value & 3;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
+    else if (!strcmp(name, "fast_var")) g_fast_var = value & 7;
     else return CLB_EINVAL;
     return CLB_OK;
 }
@@ -139,6 +140,8 @@ int clb_get_param(const char* name, int* value) {
     else if (!strcmp(name, "last_match_path")) *value = g_last_match_path;
     else if (!strcmp(name, "last_match_balanced")) *value = g_last_match_balanced;
     else if (!strcmp(name, "match_balance")) *value = g_match_balance;
+    else if (!strcmp(name, "fast_var")) *value = g_fast_var;
+    else if (!strcmp(name, "latch_var")) *value = g_latch_var;
     else return CLB_EINVAL;
     return CLB_OK;
 }

@@ -27,6 +27,8 @@ static constexpr int FT_CW = FT_TW + 2, FT_CH = FT_TH + 2;   // score region: +-
 static constexpr int FT_CSTRIDE = 68;
 
 int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
+int g_fast_var = 7;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
+                      // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16; 0 = the first-generation path
 
 struct RowMap {   // global row index <-> (level, y)
     int n; int row_base[CLB_MAX_LEVELS + 1];
@@ -278,6 +280,284 @@ angle_kernel(const LevelTable lt, clb_keypoint* __restrict__ kps, const int* __r
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// v2 score kernel: the same arithmetic on DENSE warps.  On textured frames ~10 % of the positions pass the cardinal
+// pre-test and ~3 % are corners, so in the one-pass kernel nearly every warp pays for the ring masks and the sliding
+// min/max of a few lanes.  Here each stage compacts its survivors into a shared-memory queue (ballot + one shared
+// atomic per warp) and the next stage runs one survivor per thread:
+//   stage    (TH+8) x 80 pixels, 8-byte loads on interior tiles
+//   pre-test every position of the (TW+2) x (TH+2) score region: min(max(N,S), max(E,W)) > p+t or the dark twin
+//            (two adjacent compass points = one vertical and one horizontal one)            -> queue 1
+//   ring     queue 1: 16-bit bright/dark masks, 9-run test                                   -> queue 2
+//   score    queue 2: sliding min/max of width 9, score byte into the shared score map
+//   nms      queue 2 again: 8 neighbours of each corner of the output tile, survivors into the output map + row counts
+//   output   one 32-bit word (4 px) per thread to the global map
+template <int TH>
+struct Fast2 {
+    static constexpr int SH = TH + 8;              // staged rows: gy = y0 - 4 + r
+    static constexpr int SSTR = 80;                // staged cols: gx = x0 - 8 + j
+    static constexpr int CW = FT_TW + 2, CH = TH + 2;   // score region: gx = x0 - 1 + c, gy = y0 - 1 + r
+    static constexpr int CSTR = 72;                // score byte (r, c) at r * CSTR + c + 3: output col 0 is word aligned
+    static constexpr int NPOS = CH * CW;
+};
+
+__device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int stride, int (&ring)[16]) {
+    ring[0] = p[3 * stride];      ring[1] = p[3 * stride + 1];  ring[2] = p[2 * stride + 2];   ring[3] = p[stride + 3];
+    ring[4] = p[3];               ring[5] = p[-stride + 3];     ring[6] = p[-2 * stride + 2];  ring[7] = p[-3 * stride + 1];
+    ring[8] = p[-3 * stride];     ring[9] = p[-3 * stride - 1]; ring[10] = p[-2 * stride - 2]; ring[11] = p[-stride - 3];
+    ring[12] = p[-3];             ring[13] = p[stride - 3];     ring[14] = p[2 * stride - 2];  ring[15] = p[3 * stride - 1];
+}
+
+template <int TH>
+__global__ void __launch_bounds__(256)
+fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
+                 int do_nms, int* __restrict__ row_count) {
+    typedef Fast2<TH> F;
+    __shared__ __align__(16) uint8_t px[F::SH * F::SSTR];
+    __shared__ __align__(16) uint8_t sc[F::CH * F::CSTR];
+    __shared__ __align__(16) uint8_t so[TH * FT_TW];
+    __shared__ uint16_t q1[F::NPOS], q2[F::NPOS];
+    __shared__ int n1, n2, rowcnt[TH];
+
+    int tile = blockIdx.x, L = 0, tx_n = 0;
+    for (; L < lt.n; ++L) {
+        tx_n = (lt.w[L] + FT_TW - 1) / FT_TW;
+        const int cnt = tx_n * ((lt.h[L] + TH - 1) / TH);
+        if (tile < cnt) break;
+        tile -= cnt;
+    }
+    if (L >= lt.n) return;
+    const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
+    const uint8_t* __restrict__ img = lt.img[L];
+    const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * TH;
+    const int tid = threadIdx.x, lane = tid & 31;
+
+    if (tid == 0) { n1 = 0; n2 = 0; }
+    if (tid < TH) rowcnt[tid] = 0;
+    for (int i = tid; i < F::CH * F::CSTR / 4; i += 256) reinterpret_cast<uint32_t*>(sc)[i] = 0u;
+    for (int i = tid; i < TH * FT_TW / 4; i += 256) reinterpret_cast<uint32_t*>(so)[i] = 0u;
+
+    // stage
+    const bool wide = x0 >= 8 && x0 + F::SSTR - 8 <= w && (stride & 7) == 0 && (reinterpret_cast<uintptr_t>(img) & 7) == 0;
+    if (wide) {
+        for (int i = tid; i < F::SH * 10; i += 256) {          // x0 - 8 is 8-byte aligned
+            const int r = i / 10, q = i - r * 10;
+            const int gy = min(max(y0 - 4 + r, 0), h - 1);
+            const uint2 v = __ldg(reinterpret_cast<const uint2*>(img + (size_t)gy * stride + (x0 - 8)) + q);
+            *reinterpret_cast<uint2*>(&px[r * F::SSTR + q * 8]) = v;
+        }
+    } else {
+        for (int i = tid; i < F::SH * (F::SSTR / 4); i += 256) {
+            const int r = i / (F::SSTR / 4), cq = i - r * (F::SSTR / 4);
+            const int gy = min(max(y0 - 4 + r, 0), h - 1);
+            const int gx = x0 - 8 + cq * 4;
+            const uint8_t* row = img + (size_t)gy * stride;
+            uint32_t v;
+            if (gx >= 0 && gx + 3 < w && ((reinterpret_cast<uintptr_t>(row + gx)) & 3) == 0) {
+                v = __ldg(reinterpret_cast<const uint32_t*>(row + gx));
+            } else {
+                v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v |= (uint32_t)__ldg(row + min(max(gx + k, 0), w - 1)) << (8 * k);
+            }
+            *reinterpret_cast<uint32_t*>(&px[r * F::SSTR + cq * 4]) = v;
+        }
+    }
+    __syncthreads();
+
+    // pre-test -> q1
+    for (int base = 0; base < F::NPOS; base += 256) {
+        const int i = base + tid;
+        bool cand = false;
+        if (i < F::NPOS) {
+            const int r = i / F::CW, c = i - r * F::CW;
+            const int gx = x0 - 1 + c, gy = y0 - 1 + r;
+            if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3) {
+                const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+                const int cv = p[0];
+                const int pn = p[-3 * F::SSTR], ps = p[3 * F::SSTR], pe = p[3], pw = p[-3];
+                const int bright = min(max(pn, ps), max(pe, pw));
+                const int dark = max(min(pn, ps), min(pe, pw));
+                cand = (bright > cv + thresh) | (dark < cv - thresh);
+            }
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, cand);
+        if (bal) {
+            int b = 0;
+            if (lane == 0) b = atomicAdd(&n1, __popc(bal));
+            b = __shfl_sync(0xFFFFFFFFu, b, 0);
+            if (cand) q1[b + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+        }
+    }
+    __syncthreads();
+
+    // ring masks + 9-run test -> q2
+    const int c1 = n1;
+    for (int base = 0; base < c1; base += 256) {
+        const int k = base + tid;
+        bool corner = false;
+        int i = 0;
+        if (k < c1) {
+            i = q1[k];
+            const int r = i / F::CW, c = i - r * F::CW;
+            const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+            const int cv = p[0];
+            const int hi = cv + thresh, lo = cv - thresh;
+            int ring[16];
+            fast_ring(p, F::SSTR, ring);
+            uint32_t mb = 0, md = 0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { mb |= (uint32_t)(ring[j] > hi) << j; md |= (uint32_t)(ring[j] < lo) << j; }
+            auto run9 = [](uint32_t m) {
+                m |= m << 16;
+                uint32_t a = m & (m >> 1);
+                a &= a >> 2;
+                a &= a >> 4;
+                a &= m >> 8;
+                return (a & 0xFFFFu) != 0;
+            };
+            corner = run9(mb) | run9(md);
+        }
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, corner);
+        if (bal) {
+            int b = 0;
+            if (lane == 0) b = atomicAdd(&n2, __popc(bal));
+            b = __shfl_sync(0xFFFFFFFFu, b, 0);
+            if (corner) q2[b + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)i;
+        }
+    }
+    __syncthreads();
+
+    // score (KFAST.h:304-374): max(c - min_arcs(max_k x_k), max_arcs(min_k x_k) - c), sliding windows of 9 on the ring
+    const int c2 = n2;
+    for (int k = tid; k < c2; k += 256) {
+        const int i = q2[k];
+        const int r = i / F::CW, c = i - r * F::CW;
+        const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+        const int cv = p[0];
+        int ring[16];
+        fast_ring(p, F::SSTR, ring);
+        int mn1[16], mx1[16], mn2[16], mx2[16], mn4[16], mx4[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { mn1[j] = min(ring[j], ring[(j + 1) & 15]); mx1[j] = max(ring[j], ring[(j + 1) & 15]); }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { mn2[j] = min(mn1[j], mn1[(j + 2) & 15]); mx2[j] = max(mx1[j], mx1[(j + 2) & 15]); }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { mn4[j] = min(mn2[j], mn2[(j + 4) & 15]); mx4[j] = max(mx2[j], mx2[(j + 4) & 15]); }
+        int lo_of_max = 255, hi_of_min = 0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            lo_of_max = min(lo_of_max, max(mx4[j], ring[(j + 8) & 15]));
+            hi_of_min = max(hi_of_min, min(mn4[j], ring[(j + 8) & 15]));
+        }
+        const int dark = cv - lo_of_max, bright = hi_of_min - cv;
+        sc[r * F::CSTR + c + 3] = (uint8_t)((dark > bright ? dark : bright) & 0xFF);
+    }
+    __syncthreads();
+
+    // NMS (KFAST.h:484-495) over the corners of the output tile: strictly greater than the 8 neighbours' scores
+    for (int k = tid; k < c2; k += 256) {
+        const int i = q2[k];
+        const int r = i / F::CW, c = i - r * F::CW;
+        if (r < 1 || r > TH || c < 1 || c > FT_TW) continue;            // halo of the score region
+        const uint8_t* s1 = &sc[r * F::CSTR + c + 3];
+        const int s = s1[0];
+        bool keep = s != 0;
+        if (keep && do_nms)
+            keep = (s > s1[-1]) & (s > s1[1]) &
+                   (s > s1[-F::CSTR - 1]) & (s > s1[-F::CSTR]) & (s > s1[-F::CSTR + 1]) &
+                   (s > s1[F::CSTR - 1]) & (s > s1[F::CSTR]) & (s > s1[F::CSTR + 1]);
+        if (keep && x0 + c - 1 < w && y0 + r - 1 < h) {
+            so[(r - 1) * FT_TW + (c - 1)] = (uint8_t)s;
+            atomicAdd(&rowcnt[r - 1], 1);
+        }
+    }
+    __syncthreads();
+
+    // output: 4 px per thread (the map's row stride is stride[0], 128-byte aligned, >= every tile's right edge)
+    const int grow0 = rm.row_base[L];
+    const int mstride = lt.stride[0];
+    for (int i = tid; i < TH * (FT_TW / 4); i += 256) {
+        const int r = i / (FT_TW / 4), cw = i - r * (FT_TW / 4);
+        const int gx = x0 + cw * 4, gy = y0 + r;
+        if (gy < h && gx < w) {
+            const uint32_t v = reinterpret_cast<const uint32_t*>(so)[i];
+            uint8_t* dst = nms_map + (size_t)(grow0 + gy) * mstride + gx;
+            if (gx + 3 < mstride) *reinterpret_cast<uint32_t*>(dst) = v;
+            else for (int b = 0; b < 4 && gx + b < w; ++b) dst[b] = (uint8_t)(v >> (8 * b));
+        }
+    }
+    if (tid < TH && rowcnt[tid]) atomicAdd(&row_count[grow0 + y0 + tid], rowcnt[tid]);
+}
+
+// v2 tail: row offsets (sum of the counts of all earlier rows, computed by every block for itself -- a few
+// thousand ints out of L2), ordered compaction, orientation of the row's keypoints, total.  One launch instead of three.
+__global__ void __launch_bounds__(256)
+compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__ nms_map,
+                const int* __restrict__ row_count, clb_keypoint* __restrict__ kps, int cap, int* __restrict__ total) {
+    __shared__ int wsum[8];
+    __shared__ int rcnt[8];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nrows = rm.row_base[rm.n];
+    const int grow0 = blockIdx.x * 8, grow = grow0 + wid;
+    int acc = 0;
+    for (int i = tid; i < grow0; i += 256) acc += __ldg(row_count + i);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    if (lane == 0) { wsum[wid] = acc; rcnt[wid] = grow < nrows ? __ldg(row_count + grow) : 0; }
+    __syncthreads();
+    int out = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { out += wsum[k]; if (k < wid) out += rcnt[k]; }
+    const int mine = rcnt[wid];
+    if (grow == nrows - 1 && lane == 0) *total = out + mine;
+    if (grow >= nrows || mine == 0) return;
+    int L = 0;
+    while (L + 1 < rm.n && grow >= rm.row_base[L + 1]) ++L;
+    const int y = grow - rm.row_base[L];
+    const int w = lt.w[L];
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(nms_map + (size_t)grow * lt.stride[0]);
+    const int first = out;
+    for (int xb = 0; xb < w; xb += 128) {
+        const int x0 = xb + lane * 4;
+        uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;
+        if (x0 + 3 >= w) {
+            const int keep = w - x0;
+            v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - keep)))) : 0u;
+        }
+        const uint32_t any = __ballot_sync(0xFFFFFFFFu, v != 0u);
+        if (!any) continue;
+        const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
+        uint32_t pre = nz;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+        int pos = out + (int)(pre - nz);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t s = (v >> (8 * k)) & 0xFFu;
+            if (s) {
+                if (pos < cap) {
+                    clb_keypoint kp;
+                    kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)s; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
+                    kp.angle = 0.f;
+                    kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
+                    kps[pos] = kp;
+                }
+                ++pos;
+            }
+        }
+        out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+    }
+    __syncwarp();
+    // orientation (FeatureAngle.h:197-247), one lane per keypoint of this row
+    const uint8_t* __restrict__ img = lt.img[L];
+    const int stride = lt.stride[L];
+    for (int j = first + lane; j < first + mine && j < cap; j += 32) {
+        const int x = *reinterpret_cast<volatile int*>(&kps[j].x);
+        kps[j].angle = feature_angle(img, x, y, stride);
+    }
+}
+
 static RowMap make_rowmap(const LevelTable& lt) {
     RowMap rm; rm.n = lt.n; rm.row_base[0] = 0;
     for (int i = 0; i < lt.n; ++i) rm.row_base[i + 1] = rm.row_base[i] + lt.h[i];
@@ -306,15 +586,30 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     int tiles = 0;
     for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
     timer("fast").begin(s);
-    fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+    if (g_fast_var & 1) {
+        if (g_fast_var & 4) {
+            int tiles32 = 0;
+            for (int L = 0; L < lt.n; ++L) tiles32 += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + 31) / 32);
+            fast_nms2_kernel<32><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+        } else {
+            fast_nms2_kernel<16><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+        }
+    } else {
+        fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+    }
     CLB_LAUNCHED();
-    row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);
-    CLB_LAUNCHED();
-    compact_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, row_off, d_kps, cap);
-    CLB_LAUNCHED();
-    angle_kernel<<<296, 256, 0, s>>>(lt, d_kps, d_total, cap);
+    if (g_fast_var & 2) {
+        compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total);
+        CLB_LAUNCHED();
+    } else {
+        row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);
+        CLB_LAUNCHED();
+        compact_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, row_off, d_kps, cap);
+        CLB_LAUNCHED();
+        angle_kernel<<<296, 256, 0, s>>>(lt, d_kps, d_total, cap);
+        CLB_LAUNCHED();
+    }
     timer("fast").end(s);
-    CLB_LAUNCHED();
     return CLB_OK;
 }
 

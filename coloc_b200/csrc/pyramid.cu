@@ -16,8 +16,22 @@ namespace clb {
 static constexpr int RZ_TX = 32, RZ_TY = 8, RZ_PX = 4;     // thread block 32x8, 4 px per thread
 static constexpr int RZ_TILE_W = RZ_TX * RZ_PX;            // 128 x 8 output pixels per CTA
 
-__device__ __forceinline__ float unorm8(uint8_t v) { return __fdiv_rn((float)v, 255.0f); }
-__device__ __forceinline__ int gather_origin(float u) { return (__float2int_rn(__fmul_rn(u, 256.0f)) - 128) >> 8; }
+// The conversions below stay off the XU pipe (I2F / F2I / FRND / the FCHK of an IEEE division issue at 16 lanes per
+// clock per SM and were ~12 per output pixel: the first version of this kernel was bound by them, not by memory).
+//   unorm8       RN(v / 255.f) for v in 0..255 as q = v*r, q' = fma(fma(-255, q, v), r, q) with r = RN(1/255): one Newton
+//                correction is exactly the correctly rounded quotient for all 256 inputs (checked exhaustively in exact
+//                rational arithmetic, tools/check_unorm8.py); v -> float through the 2^23 exponent trick.
+//   floor_pos    floor of 0 <= x < 2^22 by a round-down add of 2^23 (the ulp there is 1).
+//   round_int    cvt.rni (ties to even) of |x| < 2^22 by a round-to-nearest add of 1.5 * 2^23.
+__device__ __forceinline__ float unorm8(uint32_t v) {
+    const float fv = __fsub_rn(__uint_as_float(0x4B000000u | v), 8388608.0f);
+    const float r = __uint_as_float(0x3B808081u);
+    const float q = __fmul_rn(fv, r);
+    return __fmaf_rn(__fmaf_rn(-255.0f, q, fv), r, q);
+}
+__device__ __forceinline__ float floor_pos(float x) { return __fsub_rn(__fadd_rd(x, 8388608.0f), 8388608.0f); }
+__device__ __forceinline__ int round_int(float x) { return (int)__float_as_uint(__fadd_rn(x, 12582912.0f)) - 0x4B400000; }
+__device__ __forceinline__ int gather_origin(float u) { return (round_int(__fmul_rn(u, 256.0f)) - 128) >> 8; }
 
 __global__ void __launch_bounds__(RZ_TX * RZ_TY)
 resize_levels_kernel(const LevelTable lt) {
@@ -41,7 +55,7 @@ resize_levels_kernel(const LevelTable lt) {
     if (y >= dh || xb >= dw) return;
 
     const float fy = __fmaf_rn((float)(uint32_t)y + 0.5f, f, -0.5f);
-    const float fly = floorf(fy);
+    const float fly = floor_pos(fy);          // fy, fx >= 0.5 * f - 0.5 > 0 for f >= 1
     const float wty = __fsub_rn(fy, fly), ivy = __fsub_rn(1.0f, wty);
     const int gy = gather_origin(__fadd_rn(fy, 0.5f));
     const int y0 = min(max(gy, 0), h0 - 1), y1 = min(max(gy + 1, 0), h0 - 1);
@@ -53,7 +67,7 @@ resize_levels_kernel(const LevelTable lt) {
     for (int k = 0; k < RZ_PX; ++k) {
         const int x = xb + k;
         const float fx = __fmaf_rn((float)(uint32_t)x + 0.5f, f, -0.5f);
-        const float flx = floorf(fx);
+        const float flx = floor_pos(fx);
         const float wtx = __fsub_rn(fx, flx), ivx = __fsub_rn(1.0f, wtx);
         const int gx = gather_origin(__fadd_rn(fx, 0.5f));
         const int x0 = min(max(gx, 0), w0 - 1), x1 = min(max(gx + 1, 0), w0 - 1);
@@ -62,7 +76,7 @@ resize_levels_kernel(const LevelTable lt) {
         const float xa = __fmaf_rn(ivx, p00, __fmul_rn(wtx, p10));
         const float xbv = __fmaf_rn(ivx, p01, __fmul_rn(wtx, p11));
         const float res = __fmaf_rn(__fmaf_rn(ivy, xa, __fmul_rn(wty, xbv)), 255.0f, 0.5f);
-        packed |= (__float2uint_rz(res) & 0xFFu) << (8 * k);
+        packed |= (__float_as_uint(__fadd_rd(res, 8388608.0f)) & 0xFFu) << (8 * k);   // res in [0.5, 255.5]: trunc = floor
     }
     uint8_t* o = dst + (size_t)y * ds + xb;
     if (xb + RZ_PX <= dw && (((uintptr_t)o) & 3) == 0) {

@@ -245,10 +245,15 @@ def test_pyramid_vs_oracle(clb, oracle, w, h):
 # ------------------------------------------------------------------ FAST + NMS + angle
 @pytest.mark.parametrize("w,h,thr", [(640, 480, 40), (533, 400, 40), (1067, 600, 40), (257, 193, 20), (70, 50, 10),
                                      (214, 161, 20), (9, 9, 5), (7, 7, 1), (6, 30, 5)])
-def test_fast_vs_oracle(clb, oracle, w, h, thr):
+@pytest.mark.parametrize("var", [7, 3, 1, 2, 0])     # fast_var: queued score kernel / fused tail / 64x32 tiles / first generation
+def test_fast_vs_oracle(clb, oracle, w, h, thr, var):
     img = synth.textured_frame(w, h, 3)
     det = clb.Detector(max(w, 8), max(h, 8), maxkp=w * h // 4 + 16, thresh=thr)
-    got = det.fast_nms_angle(img, level_idx=2)
+    clb.set_param("fast_var", var)
+    try:
+        got = det.fast_nms_angle(img, level_idx=2)
+    finally:
+        clb.set_param("fast_var", 7)
     ref = oracle.fast_nms(img, thr, quirk=0)
     for k in ref:
         k["angle"] = oracle.feature_angle(img, k["x"], k["y"]); k["scale"] = 2
@@ -257,13 +262,30 @@ def test_fast_vs_oracle(clb, oracle, w, h, thr):
     det.close()
 
 
-def test_fast_noise_and_flat(clb, oracle):
+@pytest.mark.parametrize("var", [7, 3, 0])
+def test_fast_noise_and_flat(clb, oracle, var):
+    # uniform noise: every position passes the pre-test, ~1/3 are corners -- the shared-memory queues of the v2 kernel run full
     det = clb.Detector(640, 480, maxkp=200000, thresh=40)
     noise = np.random.default_rng(0).integers(0, 256, (480, 640), dtype=np.uint8)
+    clb.set_param("fast_var", var)
+    try:
+        got = det.fast_nms_angle(noise)
+        ref = oracle.fast_nms(noise, 40)
+        assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
+        assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
+    finally:
+        clb.set_param("fast_var", 7)
+    det.close()
+
+
+def test_fast_threshold_zero_full_queues(clb, oracle):
+    # thresh 1 on noise: the candidate queue holds (nearly) every position of every tile
+    det = clb.Detector(200, 150, maxkp=40000, thresh=1)
+    noise = np.random.default_rng(5).integers(0, 256, (150, 200), dtype=np.uint8)
     got = det.fast_nms_angle(noise)
-    ref = oracle.fast_nms(noise, 40)
-    assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
-    assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
+    ref = oracle.fast_nms(noise, 1)
+    assert len(got) == len(ref) and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["y"], ref["y"]) \
+        and np.array_equal(got["score"], ref["score"])
     det.close()
 
 
