@@ -123,9 +123,9 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "match_balance")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_balance = value; }
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
-    else if (!strcmp(name, "latch_var")) g_latch_var = value & 3;
+    else if (!strcmp(name, "latch_var")) g_latch_var = value & 7;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
-    else if (!strcmp(name, "fast_var")) g_fast_var = value & 7;
+    else if (!strcmp(name, "fast_var")) g_fast_var = value & 15;
     else return CLB_EINVAL;
     return CLB_OK;
 }

@@ -28,7 +28,8 @@ static constexpr int FT_CSTRIDE = 68;
 
 int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
 int g_fast_var = 7;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
-                      // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16; 0 = the first-generation path
+                      // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16, bit 3 = score kernel compiled for
+                      // 8 CTAs per SM (32 registers); 0 = the first-generation path
 
 struct RowMap {   // global row index <-> (level, y)
     int n; int row_base[CLB_MAX_LEVELS + 1];
@@ -308,8 +309,8 @@ __device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int str
     ring[12] = p[-3];             ring[13] = p[stride - 3];     ring[14] = p[2 * stride - 2];  ring[15] = p[3 * stride - 1];
 }
 
-template <int TH>
-__global__ void __launch_bounds__(256)
+template <int TH, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
                  int do_nms, int* __restrict__ row_count) {
     typedef Fast2<TH> F;
@@ -518,35 +519,47 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
     const int w = lt.w[L];
     const uint32_t* row = reinterpret_cast<const uint32_t*>(nms_map + (size_t)grow * lt.stride[0]);
     const int first = out;
-    for (int xb = 0; xb < w; xb += 128) {
-        const int x0 = xb + lane * 4;
-        uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;
-        if (x0 + 3 >= w) {
-            const int keep = w - x0;
-            v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - keep)))) : 0u;
-        }
-        const uint32_t any = __ballot_sync(0xFFFFFFFFu, v != 0u);
-        if (!any) continue;
-        const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
-        uint32_t pre = nz;
+    // 128 px per step (one 32-bit load per lane); the loads of 8 steps are issued together -- the steps themselves are
+    // serialised by their ballots and scans, and one L2 round trip per step was most of this kernel's time
+    for (int xc = 0; xc < w; xc += 1024) {
+        uint32_t vv[8];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
-        int pos = out + (int)(pre - nz);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t s = (v >> (8 * k)) & 0xFFu;
-            if (s) {
-                if (pos < cap) {
-                    clb_keypoint kp;
-                    kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)s; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
-                    kp.angle = 0.f;
-                    kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
-                    kps[pos] = kp;
-                }
-                ++pos;
+        for (int j = 0; j < 8; ++j) {
+            const int x0 = xc + j * 128 + lane * 4;
+            uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;      // bytes beyond w inside the padded stride are masked
+            if (x0 + 3 >= w) {
+                const int keep = w - x0;
+                v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - keep)))) : 0u;
             }
+            vv[j] = v;
         }
-        out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const uint32_t v = vv[j];
+            const int x0 = xc + j * 128 + lane * 4;
+            const uint32_t any = __ballot_sync(0xFFFFFFFFu, v != 0u);
+            if (!any) continue;
+            const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
+            uint32_t pre = nz;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+            int pos = out + (int)(pre - nz);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t sv = (v >> (8 * k)) & 0xFFu;
+                if (sv) {
+                    if (pos < cap) {
+                        clb_keypoint kp;
+                        kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)sv; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
+                        kp.angle = 0.f;
+                        kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
+                        kps[pos] = kp;
+                    }
+                    ++pos;
+                }
+            }
+            out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+        }
     }
     __syncwarp();
     // orientation (FeatureAngle.h:197-247), one lane per keypoint of this row
@@ -590,9 +603,11 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
         if (g_fast_var & 4) {
             int tiles32 = 0;
             for (int L = 0; L < lt.n; ++L) tiles32 += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + 31) / 32);
-            fast_nms2_kernel<32><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+            if (g_fast_var & 8) fast_nms2_kernel<32, 8><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+            else fast_nms2_kernel<32, 5><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
         } else {
-            fast_nms2_kernel<16><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+            if (g_fast_var & 8) fast_nms2_kernel<16, 8><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+            else fast_nms2_kernel<16, 5><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
         }
     } else {
         fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);

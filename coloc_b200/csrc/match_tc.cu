@@ -203,6 +203,47 @@ __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0
     }
 }
 
+// v4 epilogue state in the accumulator's own domain: the two largest dot products seen (= the two smallest distances,
+// d = (512 - x) / 2) and the row of the largest.  No conversion and no key packing inside the sweep: an update is
+// 2 FMNMX + FSETP + SEL + FMNMX per element, branch-free inside a sub-group of 4.  (The packed-key version converted
+// every updating element with F2I on the XU pipe; while the per-query thresholds are still open -- the first ~100
+// tiles of a sweep, i.e. most of a frame-pair-sized call -- that path was the long pole: 4 800 cycles for the first
+// tile, ~3 200 for each of the next seven, against 1 148 in steady state.)
+struct TcStateF { float b, s; uint32_t idx; };
+
+__device__ __forceinline__ void tc_process32f(const float (&v)[32], uint32_t row0, TcStateF& st) {
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+        const float* x = &v[16 * g];
+        const float m0 = tc_max3(x[0], x[1], x[2]), m1 = tc_max3(x[3], x[4], x[5]), m2 = tc_max3(x[6], x[7], x[8]);
+        const float m3 = tc_max3(x[9], x[10], x[11]), m4 = tc_max3(x[12], x[13], x[14]);
+        const float m = tc_max3(tc_max3(m0, m1, m2), tc_max3(m3, m4, x[15]), -1e30f);
+        if (m > st.s) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float mq = fmaxf(tc_max3(x[4 * q], x[4 * q + 1], x[4 * q + 2]), x[4 * q + 3]);
+                if (mq > st.s) {          // s only rises: elements that do not beat it change nothing
+#pragma unroll
+                    for (int e = 4 * q; e < 4 * q + 4; ++e) {
+                        const float xe = x[e];
+                        st.s = fmaxf(st.s, fminf(st.b, xe));
+                        st.idx = xe > st.b ? row0 + (uint32_t)(16 * g + e) : st.idx;     // strict: the first row attaining the minimum wins
+                        st.b = fmaxf(st.b, xe);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// packed keys of a finished sweep (the format the merge kernels take): distance << 22 | row; the second key's row bits
+// are all ones so that second >= best also holds on equal distances
+__device__ __forceinline__ uint2 tc_statef_keys(const TcStateF& st) {
+    const uint32_t kb = st.b < -600.f ? 0xFFFFFFFFu : ((((uint32_t)(512 - (int)st.b)) >> 1) << TC_KEY_SHIFT) | st.idx;
+    const uint32_t ks = st.s < -600.f ? 0xFFFFFFFFu : ((((uint32_t)(512 - (int)st.s)) >> 1) << TC_KEY_SHIFT) | ((1u << TC_KEY_SHIFT) - 1u);
+    return make_uint2(kb, ks);
+}
+
 // One 128-column accumulator tile: four 32-column TMEM loads, the next one in flight while the
 // current one is scanned; the buffer is handed back to the MMA warp as soon as the last load landed.
 template <bool MASKED>
@@ -765,7 +806,7 @@ __device__ __forceinline__ void tc_mma_mxf4_ts_n64(uint32_t d_tmem, uint32_t a_t
 }
 
 template <bool MASKED>
-__device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcState& st) {
+__device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcStateF& st) {
     float v0[32], v1[32];
     tc_ld32(t, v0); tc_ld32(t + 32, v1);
     tc_wait_ld();
@@ -779,8 +820,8 @@ __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0,
             if (32 + i >= valid) v1[i] = -1e30f;
         }
     }
-    tc_process32(v0, row0, st);
-    tc_process32(v1, row0 + 32, st);
+    tc_process32f(v0, row0, st);
+    tc_process32f(v1, row0 + 32, st);
 }
 
 // One CTA of the v4 sweep: query rows [qblock*256, +256) of Q against DB tiles [tile0, tile0+ntiles) of the expanded image Tx
@@ -809,6 +850,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     long long dbg_c0 = 0; unsigned long long dbg_t0 = 0;
     if ((dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0) { dbg_c0 = clock64(); asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0)); }
+    long long dbg_c1 = 0;
 
     if (tid == 0) {
         for (int s = 0; s < TC4_STAGES; ++s) { tc_mbar_init(bar_full + 8 * s, 1); tc_mbar_init(bar_empty + 8 * s, TC_QTILES); }
@@ -824,6 +866,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (dbg == 7 && tid == 0) dbg_c1 = clock64();
     const uint32_t tmem = *tmem_slot_ptr;
     // TMEM map: 0-127 / 128-255 accumulators D_0 / D_1; 256-319 unit scale factors; 320-383 / 384-447 query tiles A_0 / A_1
     const uint32_t tm_sf = tmem + 256u, tm_a = tmem + 320u;
@@ -945,6 +988,9 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         const int e = warp - 2;
         const int quarter = warp & 3, m = (e >> 2) & 1, half = e >> 3;
         const int row = quarter * 32 + lane;
+        long long pc[6] = {0, 0, 0, 0, 0, 0};                    // dbg 7: phase clocks of epilogue warp 0
+        const bool prof = dbg == 7 && e == 0 && lane == 0 && qblock == 0 && tile0 == 0;
+        if (prof) pc[0] = clock64();
         const int qi = qblock * TC_QROWS + m * TC_TILE + row;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
         {
@@ -969,9 +1015,10 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             __syncwarp();
             if (lane == 0) tc_mbar_arrive(bar_a);
         }
+        if (prof) pc[1] = clock64();
         const uint32_t tbase = lane_base + (uint32_t)(m * TC_TILE + half * 64);
         const uint32_t hb = (uint32_t)(16 * m + (split ? 8 * half : 0));      // this warp's hand-off barriers
-        TcState st; st.best = 0xFFFFFFFFu; st.second = 0xFFFFFFFFu; st.thr = -1e30f;
+        TcStateF st; st.b = -1e30f; st.s = -1e30f; st.idx = 0u;
         if (dbg == 15 || dbg == 16) {      // timing experiment: bare TMEM read stream (16: only query tile 0's warps)
             float acc = 0.f;
             if (dbg == 15 || m == 0)
@@ -982,7 +1029,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
 #pragma unroll
                     for (int i = 0; i < 32; ++i) acc += v0[i] + v1[i];
                 }
-            if (acc == 12345.678f) st.best = 0u;
+            if (acc == 12345.678f) st.idx = 1u;
         }
         for (int j = 0; j < (dbg >= 10 && dbg != 20 ? 0 : ntiles); ++j) {
             if (dbg == 20) tc_mbar_spin(bar_tfull + hb, (uint32_t)(j & 1));
@@ -1002,9 +1049,10 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                 float acc = 0.f;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) acc += v0[i] + v1[i];
-                if (acc == 12345.678f) st.best = 0u;
+                if (acc == 12345.678f) st.idx = 1u;
                 continue;
             }
+            if (prof && j < 2) pc[2 + j] = clock64();
             const int valid = chunk_rows - j * TC_TILE - half * 64;       // rows of this half that exist
             const uint32_t row0 = (uint32_t)(j * TC_TILE + half * 64);
             if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + hb, lane, st);
@@ -1012,14 +1060,21 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         }
         // merge the two column halves of each query by packed key.  The staging array aliases ring stage 0, which the
         // last tile's MMAs of the OTHER query tile may still be reading: wait until every epilogue warp has seen its last tile.
+        if (prof) pc[4] = clock64();
         asm volatile("bar.sync 1, %0;" ::"n"(TC4_EPI_WARPS * 32) : "memory");
-        if (half == 1) smem_res[m * TC_TILE + row] = make_uint2(st.best, st.second);
+        const uint2 mine = tc_statef_keys(st);
+        if (half == 1) smem_res[m * TC_TILE + row] = mine;
         asm volatile("bar.sync 1, %0;" ::"n"(TC4_EPI_WARPS * 32) : "memory");
         if (half == 0 && qi < nQ) {
             const uint2 o = smem_res[m * TC_TILE + row];
-            const uint32_t b = min(st.best, o.x);
-            const uint32_t sec = min(max(st.best, o.x), min(st.second, o.y));
+            const uint32_t b = min(mine.x, o.x);
+            const uint32_t sec = min(max(mine.x, o.x), min(mine.y, o.y));
             partial_chunk[qi] = make_uint2(b, sec);
+        }
+        if (prof) {
+            pc[5] = clock64();
+            printf("tc4 phases (cycles since the epilogue warp started): queries in TMEM %lld, first accumulator %lld, second %lld, sweep done %lld, merged %lld\n",
+                   pc[1] - pc[0], pc[2] - pc[0], pc[3] - pc[0], pc[4] - pc[0], pc[5] - pc[0]);
         }
     }
 
@@ -1032,8 +1087,8 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
     if ((dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0 && qblock == 0 && tile0 == 0) {     // real SM clock while the sweep runs: cycles / globaltimer ns
         unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         const long long c1 = clock64();
-        printf("tc4 qblock %d: %lld cycles in %llu ns = %.0f MHz, %d tiles, %.1f cycles/tile\n", qblock, c1 - dbg_c0, t1 - dbg_t0,
-               1e3 * (double)(c1 - dbg_c0) / (double)(t1 - dbg_t0), ntiles, (double)(c1 - dbg_c0) / ntiles);
+        printf("tc4 qblock %d: %lld cycles in %llu ns = %.0f MHz, %d tiles, %.1f cycles/tile; barriers + TMEM allocation %lld cycles\n", qblock, c1 - dbg_c0, t1 - dbg_t0,
+               1e3 * (double)(c1 - dbg_c0) / (double)(t1 - dbg_t0), ntiles, (double)(c1 - dbg_c0) / ntiles, dbg_c1 - dbg_c0);
     }
 }
 

@@ -1,5 +1,6 @@
 """A/B timing of the describe kernel: texture vs LDG gather x kernel variants (python tools/latch_ab.py [w h])
-latch_var bit 0 = block-shaped gather + lane transpose, bit 1 = schedule table in shared memory"""
+latch_var bit 0 = block-shaped gather + lane transpose, bit 1 = schedule table in shared memory,
+bit 2 = single gather path (clamp min/max for every keypoint)"""
 import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -13,7 +14,7 @@ clb.set_timing(True)
 ref = None
 for rep in range(2):
     for tex in (0, 1):
-        for var in (0, 1, 2, 3):
+        for var in (0, 1, 2, 3, 7):
             clb.set_param("latch_tex", tex)
             clb.set_param("latch_var", var)
             ts = []
