@@ -212,22 +212,23 @@ __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0
 struct TcStateF { float b, s; uint32_t idx; };
 
 __device__ __forceinline__ void tc_process32f(const float (&v)[32], uint32_t row0, TcStateF& st) {
+    // maxima of the eight sub-groups of 4 first (independent: they pipeline), then one test per group of 16 and, behind it,
+    // one per sub-group: the update path re-uses the sub-group maxima instead of recomputing them
+    float mq[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) mq[q] = fmaxf(tc_max3(v[4 * q], v[4 * q + 1], v[4 * q + 2]), v[4 * q + 3]);
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
-        const float* x = &v[16 * g];
-        const float m0 = tc_max3(x[0], x[1], x[2]), m1 = tc_max3(x[3], x[4], x[5]), m2 = tc_max3(x[6], x[7], x[8]);
-        const float m3 = tc_max3(x[9], x[10], x[11]), m4 = tc_max3(x[12], x[13], x[14]);
-        const float m = tc_max3(tc_max3(m0, m1, m2), tc_max3(m3, m4, x[15]), -1e30f);
+        const float m = fmaxf(tc_max3(mq[4 * g], mq[4 * g + 1], mq[4 * g + 2]), mq[4 * g + 3]);
         if (m > st.s) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float mq = fmaxf(tc_max3(x[4 * q], x[4 * q + 1], x[4 * q + 2]), x[4 * q + 3]);
-                if (mq > st.s) {          // s only rises: elements that do not beat it change nothing
+            for (int q = 4 * g; q < 4 * g + 4; ++q) {
+                if (mq[q] > st.s) {       // s only rises: elements that do not beat it change nothing
 #pragma unroll
                     for (int e = 4 * q; e < 4 * q + 4; ++e) {
-                        const float xe = x[e];
+                        const float xe = v[e];
                         st.s = fmaxf(st.s, fminf(st.b, xe));
-                        st.idx = xe > st.b ? row0 + (uint32_t)(16 * g + e) : st.idx;     // strict: the first row attaining the minimum wins
+                        st.idx = xe > st.b ? row0 + (uint32_t)e : st.idx;     // strict: the first row attaining the minimum wins
                         st.b = fmaxf(st.b, xe);
                     }
                 }
@@ -1135,11 +1136,12 @@ int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, 
     return CLB_OK;
 }
 
-// CTA time model (us) fitted to tools/tc_small.py sweeps: ~28 us of prologue (TMEM allocation, query expansion, barriers), 0.60 us
-// per DB tile in steady state, and 0.16 us more per tile over the first ~200 tiles while the per-query thresholds are still open
-// and most 16-column groups take the update path (54 tiles: 69 us, 161: 150 us, 5 208: 3.3 ms)
+// CTA time model (us) fitted to one-wave sweeps (tools/tc_phases.py: 8 tiles 22.9 us, 32: 45.5, 84: 84.2, 160: 135.3): ~15 us of
+// launch + prologue (TMEM allocation, query expansion, first operands) + tail, 0.65 us per DB tile in steady state, and 0.29 us
+// more per tile over the first ~50 tiles while the per-query thresholds are still open and most groups take the update path.
+// (Before the float-domain epilogue state the same fit gave 28 us + 0.60 + 0.157 over the first 200 tiles.)
 double tc_cta_cost_us(int tiles) {
-    return 28.0 + 0.60 * (double)tiles + 0.157 * (double)(tiles < 200 ? tiles : 200);
+    return 15.4 + 0.65 * (double)tiles + 0.29 * (double)(tiles < 50 ? tiles : 50);
 }
 
 // choose the DB chunk count: fewest chunks whose CTA count fills whole waves of `sm_count` SMs
@@ -1227,7 +1229,7 @@ double tc_balanced_cost_us(long long units, long long strips, int sm_count, long
     if (units <= 0) return 0.0;
     const long long quota = (units + parts - 1) / parts;
     const double extra_jobs = (double)(strips < parts ? strips : parts) / (double)parts;
-    return 1.03 * (tc_cta_cost_us((int)quota) + 28.0 * extra_jobs);
+    return 1.03 * (tc_cta_cost_us((int)quota) + 12.0 * extra_jobs);   // a job that starts mid-range: prologue + part of the warm-up again
 }
 
 int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s) {
