@@ -14,6 +14,8 @@ if what in ("match", "matchfull"):
     T = torch.from_numpy(synth.random_descriptors(nt, 42).view(np.int64)).cuda()
     Q = torch.from_numpy(synth.random_descriptors(nq, 43).view(np.int64)).cuda()
     m = clb.Matcher(maxkp=nt); out = torch.zeros((3, nq), dtype=torch.int32, device="cuda")
+    if os.environ.get("CLB_TC_CHUNKS"):          # force the DB chunk count (experiments on the chunk size vs L2)
+        clb.set_param("match_balance", 0); clb.set_param("match_tc_chunks", int(os.environ["CLB_TC_CHUNKS"]))
     for _ in range(4):
         m.match_dev(Q, nq, T, nt, 60, out[0], out[1], out[2], stream=torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
