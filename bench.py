@@ -176,7 +176,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": v, "unit": "comparisons/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "comparisons/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -634,10 +634,32 @@ def run_ours(args, rank, world, local_rank):
                 line["extra"][key] = stream_extra(clb, torch, synth, *a)
             except Exception as e:
                 line["extra"][key + "_error"] = repr(e)
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
+
+
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """stdout carries exactly ONE line, the JSON: everything else any library writes to fd 1 -- NCCL prints its version banner
+    there at NCCL_DEBUG=WARN/VERSION/INFO -- is sent to stderr for the lifetime of the process."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(text):
+    sys.stdout.flush()
+    data = (text + "\n").encode()
+    fd = _REAL_STDOUT if _REAL_STDOUT is not None else 1
+    while data:
+        data = data[os.write(fd, data):]
 
 
 def main():
+    guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -650,8 +672,6 @@ def main():
         run_reference(args, rank, world)
         return
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         import torch
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
