@@ -13,8 +13,9 @@
 
 namespace clb {
 
-static constexpr int RZ_TX = 32, RZ_TY = 8, RZ_PX = 4;     // thread block 32x8, 4 px per thread
-static constexpr int RZ_TILE_W = RZ_TX * RZ_PX;            // 128 x 8 output pixels per CTA
+static constexpr int RZ_TX = 32, RZ_TY = 4, RZ_PX = 4, RZ_ROWS = 2;   // thread block 32x4, 4 px x 2 rows per thread
+static constexpr int RZ_TILE_W = RZ_TX * RZ_PX;                       // 128 x 8 output pixels per CTA
+static constexpr int RZ_TILE_H = RZ_TY * RZ_ROWS;
 
 // The conversions below stay off the XU pipe (I2F / F2I / FRND / the FCHK of an IEEE division issue at 16 lanes per
 // clock per SM and were ~12 per output pixel: the first version of this kernel was bound by them, not by memory).
@@ -39,7 +40,7 @@ resize_levels_kernel(const LevelTable lt) {
     int tile = blockIdx.x, L = 1, tx_n = 0;
     for (; L < lt.n; ++L) {
         tx_n = (lt.w[L] + RZ_TILE_W - 1) / RZ_TILE_W;
-        const int cnt = tx_n * ((lt.h[L] + RZ_TY - 1) / RZ_TY);
+        const int cnt = tx_n * ((lt.h[L] + RZ_TILE_H - 1) / RZ_TILE_H);
         if (tile < cnt) break;
         tile -= cnt;
     }
@@ -50,46 +51,55 @@ resize_levels_kernel(const LevelTable lt) {
     const int dw = lt.w[L], dh = lt.h[L], ds = lt.stride[L];
     const float f = lt.f[L];
 
-    const int y = (tile / tx_n) * RZ_TY + threadIdx.y;
+    const int yb = (tile / tx_n) * RZ_TILE_H + threadIdx.y * RZ_ROWS;
     const int xb = (tile % tx_n) * RZ_TILE_W + threadIdx.x * RZ_PX;
-    if (y >= dh || xb >= dw) return;
+    if (yb >= dh || xb >= dw) return;
 
-    const float fy = __fmaf_rn((float)(uint32_t)y + 0.5f, f, -0.5f);
-    const float fly = floor_pos(fy);          // fy, fx >= 0.5 * f - 0.5 > 0 for f >= 1
-    const float wty = __fsub_rn(fy, fly), ivy = __fsub_rn(1.0f, wty);
-    const int gy = gather_origin(__fadd_rn(fy, 0.5f));
-    const int y0 = min(max(gy, 0), h0 - 1), y1 = min(max(gy + 1, 0), h0 - 1);
-    const uint8_t* r0 = src + (size_t)y0 * s0;
-    const uint8_t* r1 = src + (size_t)y1 * s0;
-
-    uint32_t packed = 0;
+    // the column terms (footprint origin, weights) are computed once and serve both rows of the thread
+    uint32_t cx0[RZ_PX], cx1[RZ_PX];
+    float wtx[RZ_PX], ivx[RZ_PX];
 #pragma unroll
     for (int k = 0; k < RZ_PX; ++k) {
         const int x = xb + k;
         const float fx = __fmaf_rn((float)(uint32_t)x + 0.5f, f, -0.5f);
-        const float flx = floor_pos(fx);
-        const float wtx = __fsub_rn(fx, flx), ivx = __fsub_rn(1.0f, wtx);
+        const float flx = floor_pos(fx);          // fy, fx >= 0.5 * f - 0.5 >= 0 for f >= 1
+        wtx[k] = __fsub_rn(fx, flx); ivx[k] = __fsub_rn(1.0f, wtx[k]);
         const int gx = gather_origin(__fadd_rn(fx, 0.5f));
-        const int x0 = min(max(gx, 0), w0 - 1), x1 = min(max(gx + 1, 0), w0 - 1);
-        const float p00 = unorm8(__ldg(r0 + x0)), p10 = unorm8(__ldg(r0 + x1));
-        const float p01 = unorm8(__ldg(r1 + x0)), p11 = unorm8(__ldg(r1 + x1));
-        const float xa = __fmaf_rn(ivx, p00, __fmul_rn(wtx, p10));
-        const float xbv = __fmaf_rn(ivx, p01, __fmul_rn(wtx, p11));
-        const float res = __fmaf_rn(__fmaf_rn(ivy, xa, __fmul_rn(wty, xbv)), 255.0f, 0.5f);
-        packed |= (__float_as_uint(__fadd_rd(res, 8388608.0f)) & 0xFFu) << (8 * k);   // res in [0.5, 255.5]: trunc = floor
+        cx0[k] = (uint32_t)min(max(gx, 0), w0 - 1); cx1[k] = (uint32_t)min(max(gx + 1, 0), w0 - 1);
     }
-    uint8_t* o = dst + (size_t)y * ds + xb;
-    if (xb + RZ_PX <= dw && (((uintptr_t)o) & 3) == 0) {
-        *reinterpret_cast<uint32_t*>(o) = packed;
-    } else {
-        for (int k = 0; k < RZ_PX && xb + k < dw; ++k) o[k] = (uint8_t)(packed >> (8 * k));
+#pragma unroll
+    for (int rr = 0; rr < RZ_ROWS; ++rr) {
+        const int y = yb + rr;
+        if (y >= dh) break;
+        const float fy = __fmaf_rn((float)(uint32_t)y + 0.5f, f, -0.5f);
+        const float fly = floor_pos(fy);
+        const float wty = __fsub_rn(fy, fly), ivy = __fsub_rn(1.0f, wty);
+        const int gy = gather_origin(__fadd_rn(fy, 0.5f));
+        // 32-bit offsets into level 0 (a level is far below 4 GiB): one IMAD.WIDE.U32 per load instead of 64-bit chains
+        const uint32_t o0 = (uint32_t)min(max(gy, 0), h0 - 1) * (uint32_t)s0, o1 = (uint32_t)min(max(gy + 1, 0), h0 - 1) * (uint32_t)s0;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < RZ_PX; ++k) {
+            const float p00 = unorm8(__ldg(src + (o0 + cx0[k]))), p10 = unorm8(__ldg(src + (o0 + cx1[k])));
+            const float p01 = unorm8(__ldg(src + (o1 + cx0[k]))), p11 = unorm8(__ldg(src + (o1 + cx1[k])));
+            const float xa = __fmaf_rn(ivx[k], p00, __fmul_rn(wtx[k], p10));
+            const float xbv = __fmaf_rn(ivx[k], p01, __fmul_rn(wtx[k], p11));
+            const float res = __fmaf_rn(__fmaf_rn(ivy, xa, __fmul_rn(wty, xbv)), 255.0f, 0.5f);
+            packed |= (__float_as_uint(__fadd_rd(res, 8388608.0f)) & 0xFFu) << (8 * k);   // res in [0.5, 255.5]: trunc = floor
+        }
+        uint8_t* o = dst + (size_t)y * ds + xb;
+        if (xb + RZ_PX <= dw && (((uintptr_t)o) & 3) == 0) {
+            *reinterpret_cast<uint32_t*>(o) = packed;
+        } else {
+            for (int k = 0; k < RZ_PX && xb + k < dw; ++k) o[k] = (uint8_t)(packed >> (8 * k));
+        }
     }
 }
 
 int launch_resize(const LevelTable& lt, cudaStream_t s) {
     int tiles = 0;
     for (int L = 1; L < lt.n; ++L)
-        tiles += ((lt.w[L] + RZ_TILE_W - 1) / RZ_TILE_W) * ((lt.h[L] + RZ_TY - 1) / RZ_TY);
+        tiles += ((lt.w[L] + RZ_TILE_W - 1) / RZ_TILE_W) * ((lt.h[L] + RZ_TILE_H - 1) / RZ_TILE_H);
     if (tiles == 0) return CLB_OK;
     timer("resize").begin(s);
     resize_levels_kernel<<<tiles, dim3(RZ_TX, RZ_TY), 0, s>>>(lt);
