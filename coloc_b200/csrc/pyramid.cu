@@ -16,6 +16,7 @@ namespace clb {
 static constexpr int RZ_TX = 32, RZ_TY = 4, RZ_PX = 4, RZ_ROWS = 2;   // thread block 32x4, 4 px x 2 rows per thread
 static constexpr int RZ_TILE_W = RZ_TX * RZ_PX;                       // 128 x 8 output pixels per CTA
 static constexpr int RZ_TILE_H = RZ_TY * RZ_ROWS;
+static_assert(RZ_TX * RZ_TY == 128, "the texel table is filled 2 entries per thread");
 
 // The conversions below stay off the XU pipe (I2F / F2I / FRND / the FCHK of an IEEE division issue at 16 lanes per
 // clock per SM and were ~12 per output pixel: the first version of this kernel was bound by them, not by memory).
@@ -51,6 +52,15 @@ resize_levels_kernel(const LevelTable lt) {
     const int dw = lt.w[L], dh = lt.h[L], ds = lt.stride[L];
     const float f = lt.f[L];
 
+    // texel -> float table: the exact unorm8() of every byte value, built once per CTA (2 entries per thread); a lookup is one
+    // shared load on the otherwise idle LSU pipe instead of 5 issue slots on the ALU / FMA pipes this kernel is bound by
+    __shared__ float lut[256];
+    {
+        const int t = threadIdx.y * RZ_TX + threadIdx.x;
+        lut[t] = unorm8((uint32_t)t);
+        lut[t + RZ_TX * RZ_TY] = unorm8((uint32_t)(t + RZ_TX * RZ_TY));
+    }
+    __syncthreads();
     const int yb = (tile / tx_n) * RZ_TILE_H + threadIdx.y * RZ_ROWS;
     const int xb = (tile % tx_n) * RZ_TILE_W + threadIdx.x * RZ_PX;
     if (yb >= dh || xb >= dw) return;
@@ -80,8 +90,8 @@ resize_levels_kernel(const LevelTable lt) {
         uint32_t packed = 0;
 #pragma unroll
         for (int k = 0; k < RZ_PX; ++k) {
-            const float p00 = unorm8(__ldg(src + (o0 + cx0[k]))), p10 = unorm8(__ldg(src + (o0 + cx1[k])));
-            const float p01 = unorm8(__ldg(src + (o1 + cx0[k]))), p11 = unorm8(__ldg(src + (o1 + cx1[k])));
+            const float p00 = lut[__ldg(src + (o0 + cx0[k]))], p10 = lut[__ldg(src + (o0 + cx1[k]))];
+            const float p01 = lut[__ldg(src + (o1 + cx0[k]))], p11 = lut[__ldg(src + (o1 + cx1[k]))];
             const float xa = __fmaf_rn(ivx[k], p00, __fmul_rn(wtx[k], p10));
             const float xbv = __fmaf_rn(ivx[k], p01, __fmul_rn(wtx[k], p11));
             const float res = __fmaf_rn(__fmaf_rn(ivy, xa, __fmul_rn(wty, xbv)), 255.0f, 0.5f);
