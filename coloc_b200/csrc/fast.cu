@@ -27,9 +27,9 @@ static constexpr int FT_CW = FT_TW + 2, FT_CH = FT_TH + 2;   // score region: +-
 static constexpr int FT_CSTRIDE = 68;
 
 int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
-int g_fast_var = 7;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
+int g_fast_var = 23;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
                       // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16, bit 3 = score kernel compiled for
-                      // 8 CTAs per SM (32 registers); 0 = the first-generation path
+                      // 8 CTAs per SM (32 registers), bit 4 = pre-test on four positions per thread in 16-bit lanes; 0 = the first-generation path
 
 struct RowMap {   // global row index <-> (level, y)
     int n; int row_base[CLB_MAX_LEVELS + 1];
@@ -309,7 +309,7 @@ __device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int str
     ring[12] = p[-3];             ring[13] = p[stride - 3];     ring[14] = p[2 * stride - 2];  ring[15] = p[3 * stride - 1];
 }
 
-template <int TH, int MINB>
+template <int TH, int MINB, bool SWAR>
 __global__ void __launch_bounds__(256, MINB)
 fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
                  int do_nms, int* __restrict__ row_count) {
@@ -367,6 +367,64 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
     __syncthreads();
 
     // pre-test -> q1
+    if (SWAR) {
+        // four positions per thread, two per register in 16-bit lanes: VIMNMX.U16x2 / VIADD.16x2 are native on sm_100a (the
+        // byte-wise video intrinsics are not).  Item (r, wq) = the four score-region columns 4wq-3 .. 4wq of row r, an aligned
+        // word of the staged pixels; east / west neighbours come from the adjacent words by byte permute.
+        //   bright > p + t  <=>  bright + ~p - t      has its lane's sign bit clear   (~p = -p - 1 in a 16-bit lane)
+        //   dark   < p - t  <=>  dark   + ~p + t + 1  has its lane's sign bit set
+        constexpr int WPR = 18, NITEM = F::CH * WPR;
+        const uint32_t k_b = ((uint32_t)(-thresh) & 0xFFFFu) * 0x10001u, k_d = ((uint32_t)(thresh + 1) & 0xFFFFu) * 0x10001u;
+        const int xlo = max(3, x0 - 1), xhi = min(w - 3, x0 + F::CW - 1);      // valid gx range of this tile's score region
+        for (int base = 0; base < NITEM; base += 256) {
+            const int it = base + tid;
+            uint32_t cm = 0;
+            int r = 0, c0 = 0;
+            if (it < NITEM) {
+                r = it / WPR;
+                const int wq = it - r * WPR;
+                c0 = 4 * wq - 3;
+                const int gy = y0 - 1 + r, gxb = x0 - 1 + c0;
+                const int nlow = min(max(xlo - gxb, 0), 4), nval = min(max(xhi - gxb, 0), 4);
+                const uint32_t vmask = (0xFu << nlow) & ((1u << nval) - 1u);
+                if (gy >= 3 && gy < h - 3 && vmask) {
+                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(&px[(r + 3) * F::SSTR + 4 + 4 * wq]);
+                    const uint32_t cw = wp[0], cl = wp[-1], cr = wp[1];
+                    const uint32_t nw = wp[-3 * F::SSTR / 4], sw = wp[3 * F::SSTR / 4];
+                    const uint32_t ew = __byte_perm(cw, cr, 0x6543), ww = __byte_perm(cl, cw, 0x4321);
+                    uint32_t fl[2];
+#pragma unroll
+                    for (int hf = 0; hf < 2; ++hf) {
+                        const uint32_t sel = hf ? 0x4341u : 0x4240u;      // positions 1,3 / 0,2 -> 16-bit lanes
+                        const uint32_t c2 = __byte_perm(cw, 0u, sel), n2 = __byte_perm(nw, 0u, sel), s2 = __byte_perm(sw, 0u, sel);
+                        const uint32_t e2 = __byte_perm(ew, 0u, sel), w2 = __byte_perm(ww, 0u, sel);
+                        const uint32_t bright = __vminu2(__vmaxu2(n2, s2), __vmaxu2(e2, w2));
+                        const uint32_t dark = __vmaxu2(__vminu2(n2, s2), __vminu2(e2, w2));
+                        const uint32_t nc = ~c2;
+                        const uint32_t eb = __vadd2(bright, __vadd2(nc, k_b));
+                        const uint32_t ed = __vadd2(dark, __vadd2(nc, k_d));
+                        fl[hf] = (~eb | ed) & 0x80008000u;
+                    }
+                    const uint32_t t2 = ((fl[0] >> 15) | (fl[1] >> 14)) & 0x00030003u;   // bit 0/16: positions 0/2, bit 1/17: 1/3
+                    cm = (t2 | (t2 >> 14)) & vmask;
+                }
+            }
+            if (__ballot_sync(0xFFFFFFFFu, cm != 0u)) {
+                const uint32_t cnt = __popc(cm);
+                uint32_t pre = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+                int b = 0;
+                if (lane == 31) b = atomicAdd(&n1, (int)pre);
+                b = __shfl_sync(0xFFFFFFFFu, b, 31);
+                int pos = b + (int)(pre - cnt);
+                const int i0 = r * F::CW + c0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (cm & (1u << k)) q1[pos++] = (uint16_t)(i0 + k);
+            }
+        }
+    } else
     for (int base = 0; base < F::NPOS; base += 256) {
         const int i = base + tid;
         bool cand = false;
@@ -600,15 +658,17 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
     timer("fast").begin(s);
     if (g_fast_var & 1) {
-        if (g_fast_var & 4) {
-            int tiles32 = 0;
-            for (int L = 0; L < lt.n; ++L) tiles32 += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + 31) / 32);
-            if (g_fast_var & 8) fast_nms2_kernel<32, 8><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
-            else fast_nms2_kernel<32, 5><<<tiles32, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
-        } else {
-            if (g_fast_var & 8) fast_nms2_kernel<16, 8><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
-            else fast_nms2_kernel<16, 5><<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*);
+        static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
+            {{fast_nms2_kernel<16, 5, false>, fast_nms2_kernel<16, 5, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
+            {{fast_nms2_kernel<32, 5, false>, fast_nms2_kernel<32, 5, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
+        const int big = (g_fast_var & 4) ? 1 : 0;
+        int ntiles = tiles;
+        if (big) {
+            ntiles = 0;
+            for (int L = 0; L < lt.n; ++L) ntiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + 31) / 32);
         }
+        k2[big][(g_fast_var & 8) ? 1 : 0][(g_fast_var & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
     } else {
         fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
     }
