@@ -31,8 +31,10 @@ int g_fast_var = 23;   // clb_set_param "fast_var": bit 0 = queued score kernel 
                       // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16, bit 3 = score kernel compiled for
                       // 8 CTAs per SM (32 registers), bit 4 = pre-test on four positions per thread in 16-bit lanes; 0 = the first-generation path
 
-struct RowMap {   // global row index <-> (level, y)
+struct RowMap {   // global row index <-> (level, y); for the v2 score kernel also tile index <-> (level, tile)
     int n; int row_base[CLB_MAX_LEVELS + 1];
+    int tile_base[CLB_MAX_LEVELS + 1];      // first tile of each level for the tile height of this launch (host-computed:
+    int tiles_x[CLB_MAX_LEVELS];            // the kernel's level search is compares only, no divisions per thread)
 };
 
 __device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int stride, int t) {
@@ -320,14 +322,10 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
     __shared__ uint16_t q1[F::NPOS], q2[F::NPOS];
     __shared__ int n1, n2, rowcnt[TH];
 
-    int tile = blockIdx.x, L = 0, tx_n = 0;
-    for (; L < lt.n; ++L) {
-        tx_n = (lt.w[L] + FT_TW - 1) / FT_TW;
-        const int cnt = tx_n * ((lt.h[L] + TH - 1) / TH);
-        if (tile < cnt) break;
-        tile -= cnt;
-    }
-    if (L >= lt.n) return;
+    int L = 0;
+    while (L + 1 < rm.n && (int)blockIdx.x >= rm.tile_base[L + 1]) ++L;
+    const int tile = blockIdx.x - rm.tile_base[L], tx_n = rm.tiles_x[L];
+    if ((int)blockIdx.x >= rm.tile_base[rm.n]) return;
     const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
     const uint8_t* __restrict__ img = lt.img[L];
     const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * TH;
@@ -577,12 +575,13 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
     const int w = lt.w[L];
     const uint32_t* row = reinterpret_cast<const uint32_t*>(nms_map + (size_t)grow * lt.stride[0]);
     const int first = out;
-    // 128 px per step (one 32-bit load per lane); the loads of 8 steps are issued together -- the steps themselves are
+    // 128 px per step (one 32-bit load per lane); the loads of CB steps are issued together -- the steps themselves are
     // serialised by their ballots and scans, and one L2 round trip per step was most of this kernel's time
-    for (int xc = 0; xc < w; xc += 1024) {
-        uint32_t vv[8];
+    constexpr int CB = 16;
+    for (int xc = 0; xc < w; xc += 128 * CB) {
+        uint32_t vv[CB];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < CB; ++j) {
             const int x0 = xc + j * 128 + lane * 4;
             uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;      // bytes beyond w inside the padded stride are masked
             if (x0 + 3 >= w) {
@@ -592,7 +591,7 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
             vv[j] = v;
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < CB; ++j) {
             const uint32_t v = vv[j];
             const int x0 = xc + j * 128 + lane * 4;
             const uint32_t any = __ballot_sync(0xFFFFFFFFu, v != 0u);
@@ -632,6 +631,8 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
 static RowMap make_rowmap(const LevelTable& lt) {
     RowMap rm; rm.n = lt.n; rm.row_base[0] = 0;
     for (int i = 0; i < lt.n; ++i) rm.row_base[i + 1] = rm.row_base[i] + lt.h[i];
+    for (int i = 0; i <= CLB_MAX_LEVELS; ++i) rm.tile_base[i] = 0;
+    for (int i = 0; i < CLB_MAX_LEVELS; ++i) rm.tiles_x[i] = 0;
     return rm;
 }
 
@@ -646,7 +647,7 @@ size_t fast_scratch_bytes(const LevelTable& lt) {
 int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s) {
     if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
-    const RowMap rm = make_rowmap(lt);
+    RowMap rm = make_rowmap(lt);
     const size_t rows = rm.row_base[lt.n];
     const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
     const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
@@ -662,12 +663,12 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
         static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
             {{fast_nms2_kernel<16, 5, false>, fast_nms2_kernel<16, 5, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
             {{fast_nms2_kernel<32, 5, false>, fast_nms2_kernel<32, 5, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
-        const int big = (g_fast_var & 4) ? 1 : 0;
-        int ntiles = tiles;
-        if (big) {
-            ntiles = 0;
-            for (int L = 0; L < lt.n; ++L) ntiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + 31) / 32);
+        const int big = (g_fast_var & 4) ? 1 : 0, th = big ? 32 : 16;
+        for (int L = 0; L < lt.n; ++L) {
+            rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
+            rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + th - 1) / th);
         }
+        const int ntiles = rm.tile_base[lt.n];
         k2[big][(g_fast_var & 8) ? 1 : 0][(g_fast_var & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
     } else {
         fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
