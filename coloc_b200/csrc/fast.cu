@@ -661,8 +661,8 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     if (g_fast_var & 1) {
         typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*);
         static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
-            {{fast_nms2_kernel<16, 5, false>, fast_nms2_kernel<16, 5, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
-            {{fast_nms2_kernel<32, 5, false>, fast_nms2_kernel<32, 5, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
+            {{fast_nms2_kernel<16, 6, false>, fast_nms2_kernel<16, 6, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
+            {{fast_nms2_kernel<32, 6, false>, fast_nms2_kernel<32, 6, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
         const int big = (g_fast_var & 4) ? 1 : 0, th = big ? 32 : 16;
         for (int L = 0; L < lt.n; ++L) {
             rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
