@@ -298,6 +298,7 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
         t = torch.empty((h, w), dtype=torch.uint8).pin_memory(); t.numpy()[:] = views[i]; pins.append(t)
     maxkp = 400000 if w * h > 2000000 else 120000
     fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp)
+    INFLIGHT = int(os.environ.get("CLB_STREAM_INFLIGHT", "3"))
     m = clb.Matcher(maxkp=maxkp) if with_match else None
     # match lists are read back one frame late (two device + two pinned host buffers): the host never waits on the sweep it
     # has just queued, as a consumer that pipelines its geometric stage would not
@@ -312,7 +313,7 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
         prev = None
         pending = None                      # (buffer index, rows) of the match list still in flight
         while done < n:
-            while sub < n and fs.in_flight() < 3:
+            while sub < n and fs.in_flight() < INFLIGHT:
                 fs.submit(pins[sub % distinct].numpy(), tag=sub); sub += 1
             tag, k, d, dk, dd, cnt = fs.next(copy=False)
             nk += cnt
@@ -333,7 +334,7 @@ def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
     run(min(8, nframes))
     torch.cuda.synchronize()
     t0 = time.perf_counter(); nk, ncmp, nm = run(nframes); torch.cuda.synchronize(); dt = time.perf_counter() - t0
-    res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": 3, "keypoints_per_frame": nk / nframes,
+    res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": INFLIGHT, "keypoints_per_frame": nk / nframes,
            "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt,
            "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0)}
     if with_match:
