@@ -125,7 +125,7 @@ int clb_set_param(const char* name, int value) {
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
     else if (!strcmp(name, "latch_var")) g_latch_var = value & 7;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
-    else if (!strcmp(name, "fast_var")) g_fast_var = value & 31;
+    else if (!strcmp(name, "fast_var")) g_fast_var = value & 63;
     else return CLB_EINVAL;
     return CLB_OK;
 }

@@ -27,14 +27,16 @@ static constexpr int FT_CW = FT_TW + 2, FT_CH = FT_TH + 2;   // score region: +-
 static constexpr int FT_CSTRIDE = 68;
 
 int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
-int g_fast_var = 23;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
+int g_fast_var = 55;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
                       // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16, bit 3 = score kernel compiled for
-                      // 8 CTAs per SM (32 registers), bit 4 = pre-test on four positions per thread in 16-bit lanes; 0 = the first-generation path
+                      // 8 CTAs per SM (32 registers), bit 4 = pre-test on four positions per thread in 16-bit lanes, bit 5 = (row, tile)
+                      // occupancy bitmap: the tail visits occupied tiles only; 0 = the first-generation path
 
 struct RowMap {   // global row index <-> (level, y); for the v2 score kernel also tile index <-> (level, tile)
     int n; int row_base[CLB_MAX_LEVELS + 1];
     int tile_base[CLB_MAX_LEVELS + 1];      // first tile of each level for the tile height of this launch (host-computed:
     int tiles_x[CLB_MAX_LEVELS];            // the kernel's level search is compares only, no divisions per thread)
+    int bm_words;                           // words per row of the (row, 64-px tile) occupancy bitmap
 };
 
 __device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int stride, int t) {
@@ -314,7 +316,7 @@ __device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int str
 template <int TH, int MINB, bool SWAR>
 __global__ void __launch_bounds__(256, MINB)
 fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
-                 int do_nms, int* __restrict__ row_count) {
+                 int do_nms, int* __restrict__ row_count, uint32_t* __restrict__ bitmap) {
     typedef Fast2<TH> F;
     __shared__ __align__(16) uint8_t px[F::SH * F::SSTR];
     __shared__ __align__(16) uint8_t sc[F::CH * F::CSTR];
@@ -544,14 +546,19 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
             else for (int b = 0; b < 4 && gx + b < w; ++b) dst[b] = (uint8_t)(v >> (8 * b));
         }
     }
-    if (tid < TH && rowcnt[tid]) atomicAdd(&row_count[grow0 + y0 + tid], rowcnt[tid]);
+    if (tid < TH && rowcnt[tid]) {
+        atomicAdd(&row_count[grow0 + y0 + tid], rowcnt[tid]);
+        const int tx = tile % tx_n;          // which 64-px tiles of a row hold keypoints: the tail only visits those
+        if (bitmap) atomicOr(&bitmap[(size_t)(grow0 + y0 + tid) * rm.bm_words + (tx >> 5)], 1u << (tx & 31));
+    }
 }
 
 // v2 tail: row offsets (sum of the counts of all earlier rows, computed by every block for itself -- a few
 // thousand ints out of L2), ordered compaction, orientation of the row's keypoints, total.  One launch instead of three.
 __global__ void __launch_bounds__(256)
 compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__ nms_map,
-                const int* __restrict__ row_count, clb_keypoint* __restrict__ kps, int cap, int* __restrict__ total) {
+                const int* __restrict__ row_count, clb_keypoint* __restrict__ kps, int cap, int* __restrict__ total,
+                const uint32_t* __restrict__ bitmap) {
     __shared__ int wsum[8];
     __shared__ int rcnt[8];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -575,47 +582,75 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
     const int w = lt.w[L];
     const uint32_t* row = reinterpret_cast<const uint32_t*>(nms_map + (size_t)grow * lt.stride[0]);
     const int first = out;
-    // 128 px per step (one 32-bit load per lane); the loads of CB steps are issued together -- the steps themselves are
-    // serialised by their ballots and scans, and one L2 round trip per step was most of this kernel's time
-    constexpr int CB = 16;
-    for (int xc = 0; xc < w; xc += 128 * CB) {
-        uint32_t vv[CB];
-#pragma unroll
-        for (int j = 0; j < CB; ++j) {
-            const int x0 = xc + j * 128 + lane * 4;
-            uint32_t v = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;      // bytes beyond w inside the padded stride are masked
-            if (x0 + 3 >= w) {
-                const int keep = w - x0;
-                v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - keep)))) : 0u;
-            }
-            vv[j] = v;
+    // one step = 128 map bytes, 4 per lane, in x order: ordered emission through a warp scan of the per-lane counts
+    auto emit = [&](uint32_t v, int x0) {
+        if (x0 + 3 >= w) {                                           // bytes beyond w inside the padded stride are masked
+            const int keep = w - x0;
+            v = keep > 0 ? (v & (0xFFFFFFFFu >> (8 * (4 - min(keep, 4))))) : 0u;
         }
+        if (!__ballot_sync(0xFFFFFFFFu, v != 0u)) return;
+        const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
+        uint32_t pre = nz;
 #pragma unroll
-        for (int j = 0; j < CB; ++j) {
-            const uint32_t v = vv[j];
-            const int x0 = xc + j * 128 + lane * 4;
-            const uint32_t any = __ballot_sync(0xFFFFFFFFu, v != 0u);
-            if (!any) continue;
-            const uint32_t nz = ((v & 0xFFu) != 0) + ((v & 0xFF00u) != 0) + ((v & 0xFF0000u) != 0) + ((v >> 24) != 0);
-            uint32_t pre = nz;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+        int pos = out + (int)(pre - nz);
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
-            int pos = out + (int)(pre - nz);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t sv = (v >> (8 * k)) & 0xFFu;
-                if (sv) {
-                    if (pos < cap) {
-                        clb_keypoint kp;
-                        kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)sv; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
-                        kp.angle = 0.f;
-                        kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
-                        kps[pos] = kp;
-                    }
-                    ++pos;
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t sv = (v >> (8 * k)) & 0xFFu;
+            if (sv) {
+                if (pos < cap) {
+                    clb_keypoint kp;
+                    kp.x = x0 + k; kp.y = y; kp.score = (uint8_t)sv; kp._pad0[0] = kp._pad0[1] = kp._pad0[2] = 0;
+                    kp.angle = 0.f;
+                    kp.scale = (uint8_t)L; kp._pad1[0] = kp._pad1[1] = kp._pad1[2] = 0;
+                    kps[pos] = kp;
+                }
+                ++pos;
+            }
+        }
+        out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+    };
+    bool sparse = false;
+    const int tiles = rm.tiles_x[L];
+    if (bitmap) {                     // few occupied tiles (the usual case): visit only those, two 64-px tiles per step
+        const uint32_t* bm = bitmap + (size_t)grow * rm.bm_words;
+        const int nw = (tiles + 31) >> 5;
+        int occupied = 0;
+        for (int wi = 0; wi < nw; ++wi) occupied += __popc(__ldg(bm + wi));
+        sparse = 2 * occupied <= tiles;
+        if (sparse) {
+            int pend = -1;
+            const int sub = (lane & 15) * 4;
+            for (int wi = 0; wi < nw; ++wi) {
+                uint32_t bits = __ldg(bm + wi);                       // warp-uniform
+                while (bits) {
+                    const int t = wi * 32 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    if (pend < 0) { pend = t; continue; }
+                    const int x0 = (lane < 16 ? pend : t) * FT_TW + sub;
+                    emit(x0 < w ? __ldg(row + (x0 >> 2)) : 0u, x0);
+                    pend = -1;
                 }
             }
-            out += (int)__shfl_sync(0xFFFFFFFFu, pre, 31);
+            if (pend >= 0) {
+                const int x0 = pend * FT_TW + sub;
+                emit(lane < 16 && x0 < w ? __ldg(row + (x0 >> 2)) : 0u, x0);
+            }
+        }
+    }
+    if (!sparse) {
+        // dense rows: 128 px per step, the loads of CB steps are issued together -- the steps themselves are serialised by
+        // their ballots and scans, and one L2 round trip per step was most of this kernel's time
+        constexpr int CB = 16;
+        for (int xc = 0; xc < w; xc += 128 * CB) {
+            uint32_t vv[CB];
+#pragma unroll
+            for (int j = 0; j < CB; ++j) {
+                const int x0 = xc + j * 128 + lane * 4;
+                vv[j] = x0 < w ? __ldg(row + (x0 >> 2)) : 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < CB; ++j) emit(vv[j], xc + j * 128 + lane * 4);
         }
     }
     __syncwarp();
@@ -641,7 +676,8 @@ size_t fast_scratch_bytes(const LevelTable& lt) {
     size_t rows = 0;
     for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
     size_t map = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
-    return map + 2 * ((rows * sizeof(int) + 255) & ~(size_t)255) + 256;
+    const size_t bm_words = ((size_t)(lt.n > 0 ? (lt.w[0] + FT_TW - 1) / FT_TW : 1) + 31) / 32;
+    return map + 2 * ((rows * sizeof(int) + 255) & ~(size_t)255) + ((rows * bm_words * 4 + 255) & ~(size_t)255) + 256;
 }
 
 int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
@@ -652,14 +688,19 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
     const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
     uint8_t* nms = reinterpret_cast<uint8_t*>(scratch);
+    // [map][row_count][tile bitmap][row_off]: the counts and the bitmap are cleared by one memset
+    rm.bm_words = (int)((((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32);
+    const size_t bm_bytes = (rows * (size_t)rm.bm_words * 4 + 255) & ~(size_t)255;
     int* row_count = reinterpret_cast<int*>(nms + map_bytes);
-    int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes);
-    CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes, s));
+    uint32_t* bitmap = reinterpret_cast<uint32_t*>(nms + map_bytes + cnt_bytes);
+    int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes + bm_bytes);
+    const bool use_bm = (g_fast_var & 35) == 35;       // bit 5: the tail visits occupied tiles only (needs both v2 kernels)
+    CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes + (use_bm ? bm_bytes : 0), s));
     int tiles = 0;
     for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
     timer("fast").begin(s);
     if (g_fast_var & 1) {
-        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*);
+        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*, uint32_t*);
         static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
             {{fast_nms2_kernel<16, 6, false>, fast_nms2_kernel<16, 6, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
             {{fast_nms2_kernel<32, 6, false>, fast_nms2_kernel<32, 6, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
@@ -669,13 +710,13 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
             rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + th - 1) / th);
         }
         const int ntiles = rm.tile_base[lt.n];
-        k2[big][(g_fast_var & 8) ? 1 : 0][(g_fast_var & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+        k2[big][(g_fast_var & 8) ? 1 : 0][(g_fast_var & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count, use_bm ? bitmap : nullptr);
     } else {
         fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
     }
     CLB_LAUNCHED();
     if (g_fast_var & 2) {
-        compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total);
+        compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total, use_bm ? bitmap : nullptr);
         CLB_LAUNCHED();
     } else {
         row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);

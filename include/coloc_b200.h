@@ -290,7 +290,7 @@ int  clb_set_timing(int on);
  * "match_balance" (-1 the time model chooses, 0 uniform chunks, 1 balanced job list: the (query block) strips cut into one contiguous
  * range per SM), "match_slice_rows" (first H2D slice of the streamed host-DB path).
  * Detector side, all variants produce identical bytes: "fast_var" (bit 0 queued score kernel, bit 1 fused scan + compaction +
- * orientation, bit 2 64x32 tiles, bit 3 8 CTAs per SM, bit 4 pre-test in 16-bit lanes; default 23, 0 = first generation),
+ * orientation, bit 2 64x32 tiles, bit 3 8 CTAs per SM, bit 4 pre-test in 16-bit lanes, bit 5 tile-occupancy bitmap for the tail; default 55, 0 = first generation),
  * "latch_var" (bit 0 block-shaped gather, bit 1 schedule table in shared memory, bit 2 single gather path; default 3),
  * "latch_tex" (1 = gather through texture objects), "fast_nms" (0 = emit every corner, debug).
  * clb_get_param also answers "fast_var", "latch_var", "last_match_balanced" and "last_match_path": 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2. */

@@ -245,7 +245,7 @@ def test_pyramid_vs_oracle(clb, oracle, w, h):
 # ------------------------------------------------------------------ FAST + NMS + angle
 @pytest.mark.parametrize("w,h,thr", [(640, 480, 40), (533, 400, 40), (1067, 600, 40), (257, 193, 20), (70, 50, 10),
                                      (214, 161, 20), (9, 9, 5), (7, 7, 1), (6, 30, 5)])
-@pytest.mark.parametrize("var", [23, 19, 7, 3, 1, 2, 0])     # fast_var: queued score kernel / fused tail / 64x32 tiles / 16-bit-lane pre-test / first generation
+@pytest.mark.parametrize("var", [55, 23, 19, 7, 3, 1, 2, 0])     # fast_var: queued score kernel / fused tail / 64x32 tiles / 16-bit-lane pre-test / first generation
 def test_fast_vs_oracle(clb, oracle, w, h, thr, var):
     img = synth.textured_frame(w, h, 3)
     det = clb.Detector(max(w, 8), max(h, 8), maxkp=w * h // 4 + 16, thresh=thr)
@@ -253,7 +253,7 @@ def test_fast_vs_oracle(clb, oracle, w, h, thr, var):
     try:
         got = det.fast_nms_angle(img, level_idx=2)
     finally:
-        clb.set_param("fast_var", 23)
+        clb.set_param("fast_var", 55)
     ref = oracle.fast_nms(img, thr, quirk=0)
     for k in ref:
         k["angle"] = oracle.feature_angle(img, k["x"], k["y"]); k["scale"] = 2
@@ -262,7 +262,7 @@ def test_fast_vs_oracle(clb, oracle, w, h, thr, var):
     det.close()
 
 
-@pytest.mark.parametrize("var", [23, 7, 3, 0])
+@pytest.mark.parametrize("var", [55, 23, 7, 3, 0])
 def test_fast_noise_and_flat(clb, oracle, var):
     # uniform noise: every position passes the pre-test, ~1/3 are corners -- the shared-memory queues of the v2 kernel run full
     det = clb.Detector(640, 480, maxkp=200000, thresh=40)
@@ -274,7 +274,7 @@ def test_fast_noise_and_flat(clb, oracle, var):
         assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
         assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
     finally:
-        clb.set_param("fast_var", 23)
+        clb.set_param("fast_var", 55)
     det.close()
 
 

@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import coloc_b200 as clb
 from coloc_b200 import synth
 clb.set_timing(True)
-variants = [int(v) for v in sys.argv[1].split(",")] if len(sys.argv) > 1 else [0, 1, 2, 3, 7, 23, 31]
+variants = [int(v) for v in sys.argv[1].split(",")] if len(sys.argv) > 1 else [0, 1, 2, 3, 7, 23, 31, 55]
 for (w, h) in ((1280, 720), (3840, 2160), (641, 479), (100, 37)):
     img = synth.config_frame(w, h, 0) if w >= 640 else synth.textured_frame(w, h, 5)
     det = clb.Detector(w, h, maxkp=600000)
@@ -25,4 +25,4 @@ for (w, h) in ((1280, 720), (3840, 2160), (641, 479), (100, 37)):
             same = np.array_equal(ref[0].view(np.uint8), k.view(np.uint8)) and np.array_equal(ref[1], d)
             print(f"{w}x{h} fast_var={var}: {len(k)} kp  fast {t[1]*1e3:.1f} us  (resize {t[0]*1e3:.1f}, describe {t[2]*1e3:.1f})  same={same}", flush=True)
     det.close()
-clb.set_param("fast_var", 23)
+clb.set_param("fast_var", 55)
