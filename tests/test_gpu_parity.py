@@ -340,6 +340,28 @@ def test_detect_describe_end_to_end(clb, oracle, w, h):
     det.close()
 
 
+def test_config5_frame_end_to_end(clb, oracle):
+    # BASELINE config 5 frame size: 3840x2160 (60 tiles per row: two words of tile-occupancy bitmap per row, 32-bit level offsets
+    # beyond 8 MB, the dense and the sparse compaction path in one frame) against the oracle, keypoints and descriptors bit for bit
+    w, h = 3840, 2160
+    img = synth.config_frame(w, h, 0)
+    det = clb.Detector(w, h, maxkp=200000)
+    kps, desc = det.detect_and_describe(img)
+    okps, odesc = oracle.detect_describe(img, cap=200000)
+    assert len(kps) == len(okps) > 30000
+    assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8))
+    assert np.array_equal(desc, odesc)
+    # a mostly flat frame with a few textured islands: nearly every row takes the sparse path
+    flat = np.full((h, w), 90, np.uint8)
+    for (y0, x0) in ((100, 64), (900, 2050), (1500, 3700), (2100, 0), (40, 3776)):
+        flat[y0:y0 + 48, x0:x0 + 64] = img[y0:y0 + 48, x0:x0 + 64]
+    kps, desc = det.detect_and_describe(flat)
+    okps, odesc = oracle.detect_describe(flat, cap=200000)
+    assert len(kps) == len(okps) > 20
+    assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc, odesc)
+    det.close()
+
+
 def test_golden_frame(clb):
     g = np.load(os.path.join(GOLD, "frame168.npz"))
     det = clb.Detector(168, 126, maxkp=5000, thresh=int(g["thresh"]))
