@@ -304,6 +304,8 @@ int run_views(clb_matcher* m, const clb::PairView* v, int nv, int threshold, flo
         if (!m->jobs_ev_set) { CLB_CUDA(cudaEventCreateWithFlags(&m->jobs_ev, cudaEventDisableTiming)); m->jobs_ev_set = true; }
         CLB_CUDA(cudaEventRecord(m->jobs_ev, s));
     }
+    rc = clb_consume_pending(m, s);        // a streamed slice: its copy is waited for (and expanded) here, behind the table upload
+    if (rc) return rc;
     rc = launch_match_tc_jobs(m->jobs.as<TcJob>(), (int)njobs, s);
     if (rc) return rc;
     g_last_match_path = 4;

@@ -27,6 +27,7 @@ static int match_dispatch(clb_matcher* m, const uint64_t* dQ, int nQ, const uint
         }
     }
     g_last_match_balanced = 0;
+    { const int prc = clb_consume_pending(m, s); if (prc) return prc; }
     return launch_match(dQ, nQ, dT, nT, t_base, m->scratch.p, m->scratch.cap, m->sm_count, threshold, ratio,
                         d_match, d_best, d_second, d_partial, s, Qx, Tx);
 }
@@ -88,7 +89,7 @@ static int run_host(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* 
     return CLB_OK;
 }
 
-namespace clb { int g_match_slice_rows = 524288; }     // clb_set_param "match_slice_rows": rows of the FIRST H2D slice of the streamed host-DB path
+namespace clb { int g_match_slice_rows = 131072; }     // clb_set_param "match_slice_rows": rows of the FIRST H2D slice of the streamed host-DB path
 
 // DB rows in HOST memory: slice k+1 is copied (copy stream) while slice k is expanded and swept (caller's stream); each slice
 // leaves a per-query partial, the slices are folded in ascending row order (first-min-wins is preserved).  Slices grow
@@ -98,6 +99,9 @@ static constexpr int STREAM_MAX_SLICE = 4 << 20;
 static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* T_host, int nT, int64_t t_base,
                                   clb_partial* d_partial_out, cudaStream_t s) {
     int first = g_match_slice_rows < 1024 ? 1024 : g_match_slice_rows;
+    // a shard of a sharded map (250 k rows per GPU at 8 GPUs) is smaller than the default first slice and its whole copy would sit
+    // in front of the sweep: first slice <= a quarter of the rows, but not below 64 Ki rows (match_slice_rows >= 2^30: never cut)
+    if (first > nT / 4 && g_match_slice_rows < (1 << 30)) first = nT / 4 > 65536 ? nT / 4 : (first < 65536 ? first : 65536);
     first = (first + 127) & ~127;
     int nsl = 0, rows_max = 0;
     for (long long start = 0, sz = first; start < nT; start += sz, sz = sz * 4 > STREAM_MAX_SLICE ? STREAM_MAX_SLICE : sz * 4) {
@@ -140,15 +144,16 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
         if (k >= 2) CLB_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_rawfree[b], 0));
         CLB_CUDA(cudaMemcpyAsync(m->sraw[b].p, T_host + (size_t)start * 8, (size_t)rows * 64, cudaMemcpyHostToDevice, m->copy_stream));
         CLB_CUDA(cudaEventRecord(m->ev_copied[b], m->copy_stream));
-        CLB_CUDA(cudaStreamWaitEvent(s, m->ev_copied[b], 0));
-        const void* Tx = nullptr;
-        if (tc) {
-            rc = launch_expand(m->sraw[b].as<uint64_t>(), rows, tc_t_bytes(rows), m->sx[b].p, s);
-            if (rc) return rc;
-            Tx = m->sx[b].p;
-        }
+        // "wait for the copy, expand the slice" is handed to the sweep's launch path, which enqueues it AFTER its job-table
+        // upload: parked behind the wait, that small upload became eligible only once the next slice's copy already held the
+        // copy engine, and the sweep then sat out the whole copy (event timeline: a 0.85 ms sweep took 1.29 ms next to a
+        // 0.44 ms copy; the streamed call cost copies + sweeps)
+        const void* Tx = tc ? m->sx[b].p : nullptr;
+        m->pending.set = true; m->pending.ev = m->ev_copied[b]; m->pending.raw = m->sraw[b].as<uint64_t>(); m->pending.rows = rows;
+        m->pending.x_bytes = tc ? tc_t_bytes(rows) : 0; m->pending.x = tc ? m->sx[b].p : nullptr;
         rc = match_dispatch(m, dQ, nQ, m->sraw[b].as<uint64_t>(), rows, t_base + start, 0, 0.f, nullptr, nullptr, nullptr, parts + (size_t)k * nQ, s, Qx, Tx);
-        if (rc) return rc;
+        if (rc) { m->pending.set = false; return rc; }
+        if (m->pending.set) { rc = clb_consume_pending(m, s); if (rc) return rc; }      // a path that launched nothing
         CLB_CUDA(cudaEventRecord(m->ev_rawfree[b], s));
         start += sz;
         sz = sz * 4 > STREAM_MAX_SLICE ? STREAM_MAX_SLICE : sz * 4;
@@ -166,6 +171,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     if (!m) return CLB_ENOMEM;
     m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->mapx_ver = 0; m->stream = nullptr;
     m->jobs_host = nullptr; m->jobs_host_cap = 0; m->jobs_ev_set = false; m->stream_ready = false; m->copy_stream = nullptr;
+    m->pending.set = false;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);

@@ -23,7 +23,20 @@ struct clb_matcher {
     clb::DevBuf geo;                       // clb_model_residuals staging (geometry.cu)
     cudaEvent_t ev_copied[2], ev_rawfree[2], ev_entry;
     bool stream_ready;
+    // deferred head of a streamed slice's sweep: "wait for the slice copy, expand it" is enqueued by the sweep's launch path
+    // AFTER its job-table upload, so that the small upload is not parked behind the wait (see match_partial_streamed)
+    struct Pending { bool set; cudaEvent_t ev; const uint64_t* raw; int rows; size_t x_bytes; void* x; } pending;
 };
+
+// enqueue a pending slice head on `s` (no-op when none is pending)
+inline int clb_consume_pending(clb_matcher* m, cudaStream_t s) {
+    if (!m->pending.set) return CLB_OK;
+    m->pending.set = false;
+    cudaError_t e = cudaStreamWaitEvent(s, m->pending.ev, 0);
+    if (e != cudaSuccess) return clb::set_cuda_error(e, "cudaStreamWaitEvent", __FILE__, __LINE__);
+    if (m->pending.x) return clb::launch_expand(m->pending.raw, m->pending.rows, m->pending.x_bytes, m->pending.x, s);
+    return CLB_OK;
+}
 
 namespace clb {
 // a (query rows, expanded training set) problem of a job list (api_fmap.cu)

@@ -651,7 +651,7 @@ def test_streamed_host_db_equals_oracle(clb, oracle, tc):
         assert all(np.array_equal(out[i].cpu().numpy(), ref[i]) for i in range(3))
         m.close()
     finally:
-        clb.set_param("match_tc", -1); clb.set_param("match_slice_rows", 524288)
+        clb.set_param("match_tc", -1); clb.set_param("match_slice_rows", 131072)
 
 
 @pytest.mark.parametrize("nq,nt", [(300, 5000), (5000, 5000), (2049, 4100), (777, 12345), (20000, 20000), (130, 70000)])
