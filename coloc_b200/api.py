@@ -34,12 +34,18 @@ class MatcherOpts(C.Structure):
 
 
 def lib_path():
-    return os.path.join(HERE, "libcoloc_b200.so")
+    """libcoloc_b200.so (the product); CLB_LIB=lab selects libcoloc_b200_lab.so, the same sources built with -DCLB_LAB
+    (superseded kernel generations + variant / timing knobs, for A/B runs and the variant parity tests)."""
+    return os.path.join(HERE, "libcoloc_b200_lab.so" if os.environ.get("CLB_LIB") == "lab" else "libcoloc_b200.so")
 
 
-def build():
+def build(lab=False):
     """compile the CUDA extension in-tree (nvcc, sm_100a)."""
-    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "csrc")])
+    subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(HERE, "csrc")] + (["lab"] if lab else []))
+
+
+def is_lab():
+    return get_param("lab") == 1
 
 
 _lib = None
@@ -59,6 +65,12 @@ def lib():
         L.clb_last_kernel_ms.restype = C.c_float
         L.clb_last_kernel_ms.argtypes = [C.c_char_p]
         L.clb_set_param.argtypes = [C.c_char_p, C.c_int]
+        L.clb_detector_set_param.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.clb_stream_set_param.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.clb_sharded_set_map.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]
+        L.clb_sharded_set_map_host.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong]
+        L.clb_sharded_set_map_shard.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_longlong, C.c_int]
+        L.clb_sharded_range.argtypes = [C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -122,12 +134,19 @@ def _dptr(t):
 class Detector:
     """GPUDetector (include/coloc/GPUDetector.hpp:29-292) over the C ABI."""
 
-    def __init__(self, width, height, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0):
+    def __init__(self, width, height, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0, fast_quirk=1):
+        """fast_quirk=1 (default): FAST scans the columns the compiled reference scans (KFAST.h:243 `1 << 32` edge on 214- /
+        1286-wide levels); 0: every column (include/coloc_b200.h, clb_detector_set_param)."""
         self.opts = DetectorOpts(scale_factor, scale_levels, width, height, maxkp, thresh)
         self._h = C.c_void_p()
         _check(lib().clb_detector_create(C.byref(self.opts), int(device), C.byref(self._h)))
         self.kps = np.zeros(0, KP_DTYPE)      # last frame's raw output, as GPUDetector.hpp:32-33
         self.desc = np.zeros((0, 8), np.uint64)
+        if fast_quirk != 1:
+            self.set_param("fast_quirk", fast_quirk)
+
+    def set_param(self, name, value):
+        _check(lib().clb_detector_set_param(self._h, name.encode(), int(value)))
 
     def close(self):
         if self._h:
@@ -361,6 +380,89 @@ class Matcher:
         return int(n.value)
 
 
+class ShardedMatcher:
+    """DB-row-sharded map matching over the C ABI (clb_sharded_*; SURVEY 8e): GPUMatcher::setMapData + matchSceneWithMap /
+    matchFeaturesWithMap (GPUMatcher.hpp:110-117, 174-178, 252-271) with the map rows cut over several GPUs.
+      ShardedMatcher(devices=[0, 1, ...])                 one process drives the listed devices (peer copies of the partials)
+      ShardedMatcher(device=d, rank=r, nranks=n, uid=b)   one process per GPU; uid = ShardedMatcher.unique_id() of rank 0,
+                                                          broadcast by the caller; the exchange is one ncclAllGather per call"""
+
+    def __init__(self, devices=None, device=None, rank=0, nranks=1, uid=None, distRatio=0.8, thresh=60, maxkp=5000):
+        self.opts = MatcherOpts(distRatio, thresh, maxkp)
+        self._h = C.c_void_p()
+        if devices is not None:
+            devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+            _check(lib().clb_sharded_create(C.byref(self.opts), devs, len(devices), C.byref(self._h)))
+            self.rank_mode = False
+        else:
+            buf = C.create_string_buffer(bytes(uid), 128) if uid is not None else None
+            _check(lib().clb_sharded_create_rank(C.byref(self.opts), int(device or 0), int(rank), int(nranks), buf, C.byref(self._h)))
+            self.rank_mode = True
+        self.n = int(lib().clb_sharded_shards(self._h))
+        self._keep = None
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        _check(lib().clb_sharded_unique_id(buf))
+        return bytes(buf.raw)
+
+    def close(self):
+        if self._h:
+            lib().clb_sharded_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def shard_range(self, n_rows, shard):
+        lo, hi = C.c_longlong(0), C.c_longlong(0)
+        _check(lib().clb_sharded_range(self._h, int(n_rows), int(shard), C.byref(lo), C.byref(hi)))
+        return int(lo.value), int(hi.value)
+
+    @staticmethod
+    def _host_ptr(a):
+        if isinstance(a, np.ndarray):
+            return C.c_void_p(a.ctypes.data)
+        if isinstance(a, int):
+            return C.c_void_p(a)
+        return C.c_void_p(a.data_ptr())
+
+    def set_map(self, M, host_resident=False):
+        """the WHOLE map (numpy uint64 [n, 8] or pinned torch tensor); host_resident: rows stay in host memory and stream per call"""
+        n = int(M.shape[0])
+        if host_resident:
+            self._keep = M
+            _check(lib().clb_sharded_set_map_host(self._h, self._host_ptr(M), n))
+        else:
+            _check(lib().clb_sharded_set_map(self._h, self._host_ptr(M), n))
+
+    def set_map_shard(self, rows, row_lo, n_total, where=0):
+        """rank mode: this rank's rows only.  where: 0 host -> resident, 1 device -> resident, 2 host rows streamed per call"""
+        if where == 2:
+            self._keep = rows
+        ptr = _dptr(rows) if where == 1 else self._host_ptr(rows)
+        _check(lib().clb_sharded_set_map_shard(self._h, ptr, int(row_lo), int(rows.shape[0]), int(n_total), int(where)))
+
+    def match_map(self, Q, threshold=-1, want_dist=False, out=None):
+        """HOST queries -> HOST match[] (global map row or -1); blocking; collective in rank mode"""
+        if isinstance(Q, np.ndarray):
+            Q = np.ascontiguousarray(Q, np.uint64).reshape(-1, 8)
+        nQ = int(Q.shape[0])
+        m = out if out is not None else np.zeros(nQ, np.int32)
+        b = np.zeros(nQ, np.int32) if want_dist else None
+        s = np.zeros(nQ, np.int32) if want_dist else None
+        _check(lib().clb_sharded_match_map(self._h, self._host_ptr(Q), nQ, int(threshold), self._host_ptr(m), _ptr(b), _ptr(s)))
+        return (m, b, s) if want_dist else m
+
+    def match_map_dev(self, dQ, nQ, threshold, d_match, d_best=None, d_second=None, stream=None):
+        _check(lib().clb_sharded_match_map_dev(self._h, _dptr(dQ), int(nQ), int(threshold), _dptr(d_match), _dptr(d_best), _dptr(d_second),
+                                               _sarg(stream)))
+
+
 class FeatureMap:
     """device-side coloc::FeatureMap (idx -> Regions; GPUDetector.hpp:167-182): every frame's descriptors (and keypoints)
     stay on the GPU between detect and match (clb_fmap_*)."""
@@ -426,13 +528,15 @@ class FrameStream:
     """throughput mode of the detector (clb_stream_*): up to `depth` frames in flight, results in submission order.
     Same output as Detector.detect_and_describe, frame for frame."""
 
-    def __init__(self, width, height, depth=3, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0):
+    def __init__(self, width, height, depth=3, scale_factor=1.2, scale_levels=8, maxkp=5000, thresh=40, device=0, fast_quirk=1):
         self.opts = DetectorOpts(scale_factor, scale_levels, width, height, maxkp, thresh)
         self.depth = int(depth)
         self._h = C.c_void_p()
         L = lib()
         L.clb_stream_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64]
         _check(L.clb_stream_create(C.byref(self.opts), int(device), self.depth, C.byref(self._h)))
+        if fast_quirk != 1:
+            _check(L.clb_stream_set_param(self._h, b"fast_quirk", int(fast_quirk)))
 
     def close(self):
         if self._h:

@@ -11,8 +11,7 @@
 namespace clb {
 thread_local char g_err[512] = "";
 std::atomic<int64_t> g_launches{0};
-int g_timing = 0;
-extern int g_match_rq, g_match_hs, g_match_chunks, g_fast_nms, g_fast_var, g_match_tc, g_match_tc_chunks, g_match_tc_ver, g_match_tc_dbg, g_last_match_path, g_latch_tex, g_latch_var, g_match_slice_rows, g_match_balance, g_last_match_balanced;
+std::atomic<int> g_timing{0};
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line) {
     snprintf(g_err, sizeof(g_err), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
@@ -48,6 +47,7 @@ struct clb_detector {
     cudaStream_t copy_stream;   // keypoint D2H of the blocking per-frame call, behind the describe kernel
     cudaEvent_t ev_count;
     bool copy_ready;
+    int fast_quirk;      // 1 = the compiled reference's KFAST column walk (KFAST.h:243 `1 << 32`), 0 = every column scanned
 };
 
 static void level_dims(const clb_detector_opts& o, int w, int h, int* ws, int* hs, float* fs) {
@@ -111,37 +111,58 @@ int clb_device_count(int* n_out) { if (!n_out) return CLB_EINVAL; CLB_CUDA(cudaG
 int64_t clb_launch_count(void) { return g_launches.load(); }
 int clb_set_timing(int on) { g_timing = on; return CLB_OK; }
 float clb_last_kernel_ms(const char* which) { return which ? timer(which).ms() : 0.f; }
+// Planning knobs are process-wide atomics (set them before the calls they should affect); kernel-variant and timing knobs
+// exist in the lab build only and answer CLB_EUNSUPPORTED here otherwise, so a stray call cannot change what the product runs.
+static bool lab_knob(const char* name) {
+    static const char* const k[] = {"match_hs", "match_tc_ver", "match_tc_dbg", "latch_tex", "latch_var", "fast_nms", "fast_var"};
+    for (const char* n : k) if (!strcmp(name, n)) return true;
+    return false;
+}
 int clb_set_param(const char* name, int value) {
     if (!name) return CLB_EINVAL;
     if (!strcmp(name, "match_rq")) { if (value != 0 && value != 1 && value != 2 && value != 4) return CLB_EINVAL; g_match_rq = value; }
-    else if (!strcmp(name, "match_hs")) { if (value < 0 || value > 3) return CLB_EINVAL; g_match_hs = value; }
     else if (!strcmp(name, "match_chunks")) { if (value < 0) return CLB_EINVAL; g_match_chunks = value; }
     else if (!strcmp(name, "match_tc")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_tc = value; }
-    else if (!strcmp(name, "match_tc_ver")) { if (value < 1 || value > 4) return CLB_EINVAL; g_match_tc_ver = value; }
-    else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "match_slice_rows")) g_match_slice_rows = value < 1024 ? 1024 : value;
     else if (!strcmp(name, "match_balance")) { if (value < -1 || value > 1) return CLB_EINVAL; g_match_balance = value; }
     else if (!strcmp(name, "match_tc_chunks")) { if (value < 0) return CLB_EINVAL; g_match_tc_chunks = value; }
+#ifdef CLB_LAB
+    else if (!strcmp(name, "match_hs")) { if (value < 0 || value > 3) return CLB_EINVAL; g_match_hs = value; }
+    else if (!strcmp(name, "match_tc_ver")) { if (value < 1 || value > 4) return CLB_EINVAL; g_match_tc_ver = value; }
+    else if (!strcmp(name, "match_tc_dbg")) g_match_tc_dbg = value;
     else if (!strcmp(name, "latch_tex")) g_latch_tex = value ? 1 : 0;
     else if (!strcmp(name, "latch_var")) g_latch_var = value & 7;
     else if (!strcmp(name, "fast_nms")) g_fast_nms = value ? 1 : 0;
     else if (!strcmp(name, "fast_var")) g_fast_var = value & 63;
+#else
+    else if (lab_knob(name)) { snprintf(g_err, sizeof(g_err), "%s exists in the lab build only (make -C coloc_b200/csrc lab)", name); return CLB_EUNSUPPORTED; }
+#endif
     else return CLB_EINVAL;
     return CLB_OK;
 }
 int clb_get_param(const char* name, int* value) {
     if (!name || !value) return CLB_EINVAL;
     if (!strcmp(name, "match_rq")) *value = g_match_rq;
-    else if (!strcmp(name, "match_hs")) *value = g_match_hs;
     else if (!strcmp(name, "match_chunks")) *value = g_match_chunks;
     else if (!strcmp(name, "match_tc")) *value = g_match_tc;
-    else if (!strcmp(name, "match_tc_ver")) *value = g_match_tc_ver;
     else if (!strcmp(name, "match_tc_chunks")) *value = g_match_tc_chunks;
+    else if (!strcmp(name, "match_slice_rows")) *value = g_match_slice_rows;
     else if (!strcmp(name, "last_match_path")) *value = g_last_match_path;
     else if (!strcmp(name, "last_match_balanced")) *value = g_last_match_balanced;
     else if (!strcmp(name, "match_balance")) *value = g_match_balance;
+#ifdef CLB_LAB
+    else if (!strcmp(name, "lab")) *value = 1;
+    else if (!strcmp(name, "match_hs")) *value = g_match_hs;
+    else if (!strcmp(name, "match_tc_ver")) *value = g_match_tc_ver;
     else if (!strcmp(name, "fast_var")) *value = g_fast_var;
     else if (!strcmp(name, "latch_var")) *value = g_latch_var;
+#else
+    else if (!strcmp(name, "lab")) *value = 0;
+    else if (!strcmp(name, "match_hs")) *value = 2;
+    else if (!strcmp(name, "match_tc_ver")) *value = 4;
+    else if (!strcmp(name, "fast_var")) *value = 55;
+    else if (!strcmp(name, "latch_var")) *value = 3;
+#endif
     else return CLB_EINVAL;
     return CLB_OK;
 }
@@ -160,7 +181,7 @@ int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector*
     CLB_CUDA(cudaSetDevice(device));
     clb_detector* d = new (std::nothrow) clb_detector();
     if (!d) return CLB_ENOMEM;
-    d->o = *opts; d->device = device; d->h_total = nullptr;
+    d->o = *opts; d->device = device; d->h_total = nullptr; d->fast_quirk = 1;
     memset(&d->tex, 0, sizeof(d->tex)); d->tex_w = d->tex_h = d->tex_n = 0;
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
@@ -191,6 +212,18 @@ void clb_detector_destroy(clb_detector* d) {
     delete d;
 }
 
+int clb_detector_set_param(clb_detector* d, const char* name, int value) {
+    if (!d || !name) return CLB_EINVAL;
+    if (!strcmp(name, "fast_quirk")) { if (value != 0 && value != 1) return CLB_EINVAL; d->fast_quirk = value; return CLB_OK; }
+    snprintf(g_err, sizeof(g_err), "unknown detector parameter %s", name);
+    return CLB_EINVAL;
+}
+int clb_detector_get_param(const clb_detector* d, const char* name, int* value_out) {
+    if (!d || !name || !value_out) return CLB_EINVAL;
+    if (!strcmp(name, "fast_quirk")) { *value_out = d->fast_quirk; return CLB_OK; }
+    return CLB_EINVAL;
+}
+
 int clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, int32_t* hs, float* fs) {
     if (!d || !ws || !hs) return CLB_EINVAL;
     float tmp[CLB_MAX_LEVELS];
@@ -211,7 +244,7 @@ static int run_pipeline(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
     rc = launch_resize(lt, s);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
     if (rc) return rc;
     return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex);
 }
@@ -259,7 +292,7 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
     rc = launch_resize(lt, s);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
     if (rc) return rc;
     CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
     CLB_CUDA(cudaEventRecord(d->ev_count, s));
@@ -316,7 +349,7 @@ int clb_fast_nms_angle(clb_detector* d, const uint8_t* level, int w, int h, int 
     lt.img[0] = d->pyr.as<uint8_t>();
     CLB_CUDA(cudaMemcpy2DAsync(d->pyr.p, lt.stride[0], level, stride, w, h, cudaMemcpyHostToDevice, s));
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
     if (rc) return rc;
     CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
     CLB_CUDA(cudaStreamSynchronize(s));
@@ -437,6 +470,12 @@ int clb_stream_create(const clb_detector_opts* opts, int device, int depth, clb_
 }
 
 int clb_stream_in_flight(const clb_stream* s) { return s ? s->inflight : 0; }
+
+int clb_stream_set_param(clb_stream* s, const char* name, int value) {
+    if (!s) return CLB_EINVAL;
+    for (int i = 0; i < s->depth; ++i) { const int rc = clb_detector_set_param(s->slots[i].det, name, value); if (rc) return rc; }
+    return CLB_OK;
+}
 
 int clb_stream_submit(clb_stream* s, const uint8_t* gray, int w, int h, int stride, uint64_t tag) {
     if (!s || !gray) return CLB_EINVAL;

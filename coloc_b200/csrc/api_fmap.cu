@@ -175,7 +175,7 @@ gather_rows_kernel(const uint4* const* __restrict__ bases, const int2* __restric
 
 }  // namespace
 
-namespace clb { int g_match_balance = -1, g_last_match_balanced = 0; }
+namespace clb { std::atomic<int> g_match_balance{-1}, g_last_match_balanced{0}; }
 // g_match_balance: clb_set_param "match_balance": -1 choose by the time model, 0 uniform chunks, 1 balanced jobs
 
 // One sweep launch + one merge launch over a list of (query rows, expanded training set) views.

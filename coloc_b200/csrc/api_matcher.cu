@@ -89,7 +89,7 @@ static int run_host(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* 
     return CLB_OK;
 }
 
-namespace clb { int g_match_slice_rows = 131072; }     // clb_set_param "match_slice_rows": rows of the FIRST H2D slice of the streamed host-DB path
+namespace clb { std::atomic<int> g_match_slice_rows{131072}; }     // clb_set_param "match_slice_rows": rows of the FIRST H2D slice of the streamed host-DB path
 
 // DB rows in HOST memory: slice k+1 is copied (copy stream) while slice k is expanded and swept (caller's stream); each slice
 // leaves a per-query partial, the slices are folded in ascending row order (first-min-wins is preserved).  Slices grow
@@ -98,10 +98,11 @@ namespace clb { int g_match_slice_rows = 131072; }     // clb_set_param "match_s
 static constexpr int STREAM_MAX_SLICE = 4 << 20;
 static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* T_host, int nT, int64_t t_base,
                                   clb_partial* d_partial_out, cudaStream_t s) {
-    int first = g_match_slice_rows < 1024 ? 1024 : g_match_slice_rows;
+    const int slice_knob = g_match_slice_rows;
+    int first = slice_knob < 1024 ? 1024 : slice_knob;
     // a shard of a sharded map (250 k rows per GPU at 8 GPUs) is smaller than the default first slice and its whole copy would sit
     // in front of the sweep: first slice <= a quarter of the rows, but not below 64 Ki rows (match_slice_rows >= 2^30: never cut)
-    if (first > nT / 4 && g_match_slice_rows < (1 << 30)) first = nT / 4 > 65536 ? nT / 4 : (first < 65536 ? first : 65536);
+    if (first > nT / 4 && slice_knob < (1 << 30)) first = nT / 4 > 65536 ? nT / 4 : (first < 65536 ? first : 65536);
     first = (first + 127) & ~127;
     int nsl = 0, rows_max = 0;
     for (long long start = 0, sz = first; start < nT; start += sz, sz = sz * 4 > STREAM_MAX_SLICE ? STREAM_MAX_SLICE : sz * 4) {

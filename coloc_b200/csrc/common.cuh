@@ -14,7 +14,13 @@ namespace clb {
 
 extern thread_local char g_err[512];
 extern std::atomic<int64_t> g_launches;
-extern int g_timing;
+extern std::atomic<int> g_timing;
+// process-wide planning knobs (clb_set_param; atomics, read once per call) and diagnostics of the last call
+extern std::atomic<int> g_match_rq, g_match_chunks, g_match_tc, g_match_tc_chunks, g_match_slice_rows, g_match_balance;
+extern std::atomic<int> g_last_match_path, g_last_match_balanced;
+#ifdef CLB_LAB      // kernel-variant and timing knobs exist in the lab build only (make -C coloc_b200/csrc lab)
+extern std::atomic<int> g_match_hs, g_match_tc_ver, g_match_tc_dbg, g_latch_tex, g_latch_var, g_fast_nms, g_fast_var;
+#endif
 
 int set_cuda_error(cudaError_t e, const char* what, const char* file, int line);
 
@@ -106,7 +112,6 @@ int  tc_version();
 bool tc_needs_qx();      // v1 kernel (queries staged in shared memory) wants the expanded query image too
 int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const void* Tx, int nT, int qblocks, int nchunks, int tpc,
                            uint2* part, cudaStream_t s);
-extern int g_last_match_path;
 // batched pair lists (api_fmap.cu): one v4 CTA per TcJob, one merge row block per MergeJob; operands are E2M1 images (expand4)
 struct TcJob {
     const uint32_t* Q;        // packed query rows of the pair's slice (row 0 = first row of the slice)
@@ -137,7 +142,7 @@ int launch_resize(const LevelTable& lt, cudaStream_t s);   // fills levels 1..n-
 // fast.cu
 struct FastScratch { uint8_t* nms; int* row_count; int* row_off; int* total; };
 size_t fast_scratch_bytes(const LevelTable& lt);
-int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
+int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size_t scratch_bytes,
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s);
 // latch.cu
 int launch_describe(const LevelTable& lt, const clb_keypoint* d_kps, int n, const int* d_n, int cap,

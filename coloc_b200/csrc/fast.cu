@@ -11,7 +11,11 @@
 //   NMS     : score strictly greater than the 8 neighbours' scores              KFAST.h:484-495
 //   order   : level-major, then row-major (y, then x)                           GPUDetector.hpp:262-276
 //   angle   : fastAtan2(sum dy*I, sum dx*I) over the 37-px disc                 FeatureAngle.h:197-247
-// The `1 << 32` edge at KFAST.h:243 is given its intended meaning (all 32 columns valid).
+// The `1 << 32` edge at KFAST.h:243: on x86 the shift count wraps and the mask becomes 0, so on levels whose width has
+// (w - 38) % 16 == 0 (214 = level 6 of 640, 1286 = level 6 of 3840) the compiled reference drops the last 32 columns of every
+// row whose block walk (KFAST.h:451-459, 16-px retreat at :256-262) lands exactly on column w - 35.  `quirk` = 1 (the default,
+// clb_detector_set_param "fast_quirk") reproduces that: fast_xend_kernel replays the walk per row on the pre-test mask and the
+// score kernel stops each row at its xend; quirk = 0 gives the intended semantics (every column 3..w-4).
 //
 // Kernels: (1) score+NMS per 64x16 tile staged in shared memory, NMS'd score map + per-row counts
 // out; (2) one-block exclusive scan of the row counts; (3) warp-per-row ordered compaction that
@@ -26,19 +30,76 @@ static constexpr int FT_SSTRIDE = 80;                  // smem row stride (bytes
 static constexpr int FT_CW = FT_TW + 2, FT_CH = FT_TH + 2;   // score region: +-1
 static constexpr int FT_CSTRIDE = 68;
 
-int g_fast_nms = 1;   // debug knob: 0 = emit every corner (raw score map)
-int g_fast_var = 55;   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
+#ifdef CLB_LAB
+std::atomic<int> g_fast_nms{1};   // debug knob: 0 = emit every corner (raw score map)
+std::atomic<int> g_fast_var{55};   // clb_set_param "fast_var": bit 0 = queued score kernel (fast_nms2_kernel), bit 1 = fused scan + compaction +
                       // orientation (compact2_kernel), bit 2 = 64x32 tiles instead of 64x16, bit 3 = score kernel compiled for
                       // 8 CTAs per SM (32 registers), bit 4 = pre-test on four positions per thread in 16-bit lanes, bit 5 = (row, tile)
                       // occupancy bitmap: the tail visits occupied tiles only; 0 = the first-generation path
+#else
+static constexpr int g_fast_nms = 1, g_fast_var = 55;    // the product build carries the default variant only
+#endif
 
 struct RowMap {   // global row index <-> (level, y); for the v2 score kernel also tile index <-> (level, tile)
     int n; int row_base[CLB_MAX_LEVELS + 1];
     int tile_base[CLB_MAX_LEVELS + 1];      // first tile of each level for the tile height of this launch (host-computed:
     int tiles_x[CLB_MAX_LEVELS];            // the kernel's level search is compares only, no divisions per thread)
     int bm_words;                           // words per row of the (row, 64-px tile) occupancy bitmap
+    uint32_t quirk_mask;                    // bit L: level L takes its per-row scan end from xend[] (KFAST.h:243 edge)
 };
 
+// rows of the quirk levels laid end to end: one warp of fast_xend_kernel per row
+struct QuirkRows { int n; int level[CLB_MAX_LEVELS]; int row_base[CLB_MAX_LEVELS + 1]; };
+static constexpr int FQ_WORDS = 32;         // block bits per row: 32 words x 32 blocks x 16 px = 16 384 px wide at most
+
+__device__ __forceinline__ bool fast_pretest(const uint8_t* __restrict__ p, int stride, int t) {
+    // cardinal early-out of KFAST.h:186-235: two adjacent compass points beyond the threshold = one vertical and one horizontal
+    const int c = p[0];
+    const int pn = p[-3 * stride], ps = p[3 * stride], pe = p[3], pw = p[-3];
+    return (min(max(pn, ps), max(pe, pw)) > c + t) | (max(min(pn, ps), min(pe, pw)) < c - t);
+}
+
+// Per-row scan end of the reference's column walk (KFAST.h:451-459 with the retreat of :256-262 and the mask of :243).
+// The walk starts at column 3 and looks at 32 columns: if some pass the pre-test but none of the first 16 does it advances by
+// 16, otherwise by 32.  With B = (w - 38) / 16 blocks of 16 columns in front of column w - 35, the walk either lands on block B
+// (32 columns left -> `(1 << 32) - 1` == 0 on x86 -> the tail is dropped, xend = w - 35) or steps over it (xend = w - 3).
+// One warp per row: ballots give the "any pre-test pass" bit of each 16-column block, lane 0 replays the walk.
+__global__ void __launch_bounds__(256)
+fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int thresh, int* __restrict__ xend) {
+    __shared__ uint32_t sbits[8][FQ_WORDS];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qrow = blockIdx.x * 8 + wid;
+    if (qrow >= qr.row_base[qr.n]) return;
+    int k = 0;
+    while (k + 1 < qr.n && qrow >= qr.row_base[k + 1]) ++k;
+    const int L = qr.level[k], y = qrow - qr.row_base[k];
+    const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
+    int* out = xend + rm.row_base[L] + y;
+    if (y < 3 || y >= h - 3) { if (lane == 0) *out = w - 3; return; }
+    const uint8_t* __restrict__ row = lt.img[L] + (size_t)y * stride;
+    const int B = (w - 38) >> 4;                                  // blocks 0..B are looked at: columns 3 .. w - 20
+    uint32_t acc = 0;
+    int i = 0;
+    for (int x0 = 3; x0 <= w - 20; x0 += 32, ++i) {
+        const int x = x0 + lane;
+        const bool pass = x <= w - 20 && fast_pretest(row + x, stride, thresh);
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, pass);
+        acc |= (uint32_t)((bal & 0xFFFFu) != 0) << ((2 * i) & 31);
+        acc |= (uint32_t)((bal >> 16) != 0) << ((2 * i + 1) & 31);
+        if ((i & 15) == 15) { if (lane == 0) sbits[wid][i >> 4] = acc; acc = 0; }
+    }
+    if (lane == 0) {
+        if (i & 15) sbits[wid][i >> 4] = acc;
+        int b = 0;
+        while (b < B) {
+            const bool lo = (sbits[wid][b >> 5] >> (b & 31)) & 1u, hi = (sbits[wid][(b + 1) >> 5] >> ((b + 1) & 31)) & 1u;
+            b += (!lo && hi) ? 1 : 2;
+        }
+        *out = b == B ? w - 35 : w - 3;
+    }
+}
+
+#ifdef CLB_LAB      // first-generation kernels, kept for A/B only (clb_set_param "fast_var")
 __device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int stride, int t) {
     const int c = p[0];
     const int hi = c + t, lo = c - t;
@@ -90,7 +151,7 @@ __device__ __forceinline__ int fast_score_px(const uint8_t* __restrict__ p, int 
 
 __global__ void __launch_bounds__(256)
 fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
-                int do_nms, int* __restrict__ row_count) {
+                int do_nms, int* __restrict__ row_count, const int* __restrict__ xend) {
     __shared__ __align__(16) uint8_t px[FT_SH * FT_SSTRIDE];
     __shared__ uint8_t sc[FT_CH * FT_CSTRIDE];
 
@@ -130,7 +191,7 @@ fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __res
         const int r = i / FT_CW, c = i % FT_CW;
         const int gx = x0 - 1 + c, gy = y0 - 1 + r;
         int s = 0;
-        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3)
+        if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3 && (!((rm.quirk_mask >> L) & 1u) || gx < xend[rm.row_base[L] + gy]))
             s = fast_score_px(&px[(r + 3) * FT_SSTRIDE + (c + 3)], FT_SSTRIDE, thresh);
         sc[r * FT_CSTRIDE + c] = (uint8_t)s;
     }
@@ -193,6 +254,8 @@ row_scan_kernel(const int* __restrict__ row_count, int nrows, int* __restrict__ 
     if (tid == 0) *total = carry;
 }
 
+#endif   // CLB_LAB
+
 // FeatureAngle.h:160-177 with GCC's -O3 contraction written out (oracle-checked exhaustively)
 __device__ __forceinline__ float fast_atan2_ref(float y, float x) {
     const float PI = 3.1415927f;
@@ -229,6 +292,7 @@ __device__ __forceinline__ float feature_angle(const uint8_t* __restrict__ img, 
     return fast_atan2_ref((float)ys, (float)xs);
 }
 
+#ifdef CLB_LAB
 // one warp per global row: ordered compaction, 128 map bytes per step (one 32-bit load per lane, 4 ballots)
 __global__ void __launch_bounds__(256)
 compact_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict__ nms_map,
@@ -285,6 +349,8 @@ angle_kernel(const LevelTable lt, clb_keypoint* __restrict__ kps, const int* __r
     }
 }
 
+#endif   // CLB_LAB
+
 // ---------------------------------------------------------------------------------------------------------------
 // v2 score kernel: the same arithmetic on DENSE warps.  On textured frames ~10 % of the positions pass the cardinal
 // pre-test and ~3 % are corners, so in the one-pass kernel nearly every warp pays for the ring masks and the sliding
@@ -316,13 +382,13 @@ __device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int str
 template <int TH, int MINB, bool SWAR>
 __global__ void __launch_bounds__(256, MINB)
 fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
-                 int do_nms, int* __restrict__ row_count, uint32_t* __restrict__ bitmap) {
+                 int do_nms, int* __restrict__ row_count, uint32_t* __restrict__ bitmap, const int* __restrict__ xend) {
     typedef Fast2<TH> F;
     __shared__ __align__(16) uint8_t px[F::SH * F::SSTR];
     __shared__ __align__(16) uint8_t sc[F::CH * F::CSTR];
     __shared__ __align__(16) uint8_t so[TH * FT_TW];
     __shared__ uint16_t q1[F::NPOS], q2[F::NPOS];
-    __shared__ int n1, n2, rowcnt[TH];
+    __shared__ int n1, n2, rowcnt[TH], s_xlim[F::CH];
 
     int L = 0;
     while (L + 1 < rm.n && (int)blockIdx.x >= rm.tile_base[L + 1]) ++L;
@@ -335,6 +401,10 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
 
     if (tid == 0) { n1 = 0; n2 = 0; }
     if (tid < TH) rowcnt[tid] = 0;
+    if (tid < F::CH) {                 // scan end of each score-region row: w - 3, or the reference's column walk (fast_xend_kernel)
+        const int gy = y0 - 1 + tid;
+        s_xlim[tid] = (((rm.quirk_mask >> L) & 1u) && gy >= 3 && gy < h - 3) ? __ldg(xend + rm.row_base[L] + gy) : w - 3;
+    }
     for (int i = tid; i < F::CH * F::CSTR / 4; i += 256) reinterpret_cast<uint32_t*>(sc)[i] = 0u;
     for (int i = tid; i < TH * FT_TW / 4; i += 256) reinterpret_cast<uint32_t*>(so)[i] = 0u;
 
@@ -375,7 +445,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
         //   dark   < p - t  <=>  dark   + ~p + t + 1  has its lane's sign bit set
         constexpr int WPR = 18, NITEM = F::CH * WPR;
         const uint32_t k_b = ((uint32_t)(-thresh) & 0xFFFFu) * 0x10001u, k_d = ((uint32_t)(thresh + 1) & 0xFFFFu) * 0x10001u;
-        const int xlo = max(3, x0 - 1), xhi = min(w - 3, x0 + F::CW - 1);      // valid gx range of this tile's score region
+        const int xlo = max(3, x0 - 1);                                        // valid gx range of this tile's score region: [xlo, xhi)
         for (int base = 0; base < NITEM; base += 256) {
             const int it = base + tid;
             uint32_t cm = 0;
@@ -385,6 +455,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
                 const int wq = it - r * WPR;
                 c0 = 4 * wq - 3;
                 const int gy = y0 - 1 + r, gxb = x0 - 1 + c0;
+                const int xhi = min(s_xlim[r], x0 + F::CW - 1);
                 const int nlow = min(max(xlo - gxb, 0), 4), nval = min(max(xhi - gxb, 0), 4);
                 const uint32_t vmask = (0xFu << nlow) & ((1u << nval) - 1u);
                 if (gy >= 3 && gy < h - 3 && vmask) {
@@ -431,7 +502,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
         if (i < F::NPOS) {
             const int r = i / F::CW, c = i - r * F::CW;
             const int gx = x0 - 1 + c, gy = y0 - 1 + r;
-            if (gx >= 3 && gx < w - 3 && gy >= 3 && gy < h - 3) {
+            if (gx >= 3 && gx < s_xlim[r] && gy >= 3 && gy < h - 3) {
                 const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
                 const int cv = p[0];
                 const int pn = p[-3 * F::SSTR], ps = p[3 * F::SSTR], pe = p[3], pw = p[-3];
@@ -664,23 +735,26 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
 }
 
 static RowMap make_rowmap(const LevelTable& lt) {
-    RowMap rm; rm.n = lt.n; rm.row_base[0] = 0;
+    RowMap rm; rm.n = lt.n; rm.row_base[0] = 0; rm.bm_words = 0; rm.quirk_mask = 0;
     for (int i = 0; i < lt.n; ++i) rm.row_base[i + 1] = rm.row_base[i] + lt.h[i];
     for (int i = 0; i <= CLB_MAX_LEVELS; ++i) rm.tile_base[i] = 0;
     for (int i = 0; i < CLB_MAX_LEVELS; ++i) rm.tiles_x[i] = 0;
     return rm;
 }
 
-// scratch layout: [nms map: total_rows x stride0][row_count: total_rows ints][row_off: total_rows ints]
+// widths on which the compiled reference's `1 << 32` (KFAST.h:243) can drop a row's last 32 columns
+static inline bool fast_quirk_width(int w) { return w >= 38 && ((w - 38) & 15) == 0; }
+
+// scratch layout: [nms map: total_rows x stride0][row_count][tile bitmap][row_off][xend], the int arrays total_rows long
 size_t fast_scratch_bytes(const LevelTable& lt) {
     size_t rows = 0;
     for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
     size_t map = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
     const size_t bm_words = ((size_t)(lt.n > 0 ? (lt.w[0] + FT_TW - 1) / FT_TW : 1) + 31) / 32;
-    return map + 2 * ((rows * sizeof(int) + 255) & ~(size_t)255) + ((rows * bm_words * 4 + 255) & ~(size_t)255) + 256;
+    return map + 3 * ((rows * sizeof(int) + 255) & ~(size_t)255) + ((rows * bm_words * 4 + 255) & ~(size_t)255) + 256;
 }
 
-int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_bytes,
+int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size_t scratch_bytes,
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s) {
     if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
     RowMap rm = make_rowmap(lt);
@@ -688,34 +762,52 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
     const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
     const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
     uint8_t* nms = reinterpret_cast<uint8_t*>(scratch);
-    // [map][row_count][tile bitmap][row_off]: the counts and the bitmap are cleared by one memset
+    // [map][row_count][tile bitmap][row_off][xend]: the counts and the bitmap are cleared by one memset
     rm.bm_words = (int)((((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32);
     const size_t bm_bytes = (rows * (size_t)rm.bm_words * 4 + 255) & ~(size_t)255;
     int* row_count = reinterpret_cast<int*>(nms + map_bytes);
     uint32_t* bitmap = reinterpret_cast<uint32_t*>(nms + map_bytes + cnt_bytes);
-    int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes + bm_bytes);
-    const bool use_bm = (g_fast_var & 35) == 35;       // bit 5: the tail visits occupied tiles only (needs both v2 kernels)
+    int* xend = reinterpret_cast<int*>(nms + map_bytes + 2 * cnt_bytes + bm_bytes);
+    const int fvar = g_fast_var, fnms = g_fast_nms;
+    (void)fnms;
+    const bool use_bm = (fvar & 35) == 35;       // bit 5: the tail visits occupied tiles only (needs both v2 kernels)
     CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes + (use_bm ? bm_bytes : 0), s));
-    int tiles = 0;
-    for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
     timer("fast").begin(s);
-    if (g_fast_var & 1) {
-        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*, uint32_t*);
+    // the reference's per-row scan end on the widths its `1 << 32` bites (quirk = 1): one small launch over those levels' rows
+    QuirkRows qr; qr.n = 0; qr.row_base[0] = 0;
+    if (quirk) {
+        for (int L = 0; L < lt.n; ++L) {
+            if (!fast_quirk_width(lt.w[L]) || lt.h[L] < 7) continue;
+            if (lt.w[L] > 38 + 16 * (32 * FQ_WORDS - 1)) { snprintf(g_err, sizeof(g_err), "fast_quirk: level %d is wider than %d px", L, 38 + 16 * (32 * FQ_WORDS - 1)); return CLB_EUNSUPPORTED; }
+            rm.quirk_mask |= 1u << L;
+            qr.level[qr.n] = L; qr.row_base[qr.n + 1] = qr.row_base[qr.n] + lt.h[L]; ++qr.n;
+        }
+        if (qr.n > 0) {
+            fast_xend_kernel<<<(qr.row_base[qr.n] + 7) / 8, 256, 0, s>>>(lt, rm, qr, thresh, xend);
+            CLB_LAUNCHED();
+        }
+    }
+#ifdef CLB_LAB
+    int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes + bm_bytes);
+    if (fvar & 1) {
+        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*, uint32_t*, const int*);
         static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
             {{fast_nms2_kernel<16, 6, false>, fast_nms2_kernel<16, 6, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
             {{fast_nms2_kernel<32, 6, false>, fast_nms2_kernel<32, 6, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
-        const int big = (g_fast_var & 4) ? 1 : 0, th = big ? 32 : 16;
+        const int big = (fvar & 4) ? 1 : 0, th = big ? 32 : 16;
         for (int L = 0; L < lt.n; ++L) {
             rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
             rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + th - 1) / th);
         }
         const int ntiles = rm.tile_base[lt.n];
-        k2[big][(g_fast_var & 8) ? 1 : 0][(g_fast_var & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count, use_bm ? bitmap : nullptr);
+        k2[big][(fvar & 8) ? 1 : 0][(fvar & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, fnms, row_count, use_bm ? bitmap : nullptr, xend);
     } else {
-        fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, g_fast_nms, row_count);
+        int tiles = 0;
+        for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
+        fast_nms_kernel<<<tiles, 256, 0, s>>>(lt, rm, thresh, nms, fnms, row_count, xend);
     }
     CLB_LAUNCHED();
-    if (g_fast_var & 2) {
+    if (fvar & 2) {
         compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total, use_bm ? bitmap : nullptr);
         CLB_LAUNCHED();
     } else {
@@ -726,6 +818,16 @@ int launch_fast(const LevelTable& lt, int thresh, void* scratch, size_t scratch_
         angle_kernel<<<296, 256, 0, s>>>(lt, d_kps, d_total, cap);
         CLB_LAUNCHED();
     }
+#else
+    for (int L = 0; L < lt.n; ++L) {
+        rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
+        rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + 31) / 32);
+    }
+    fast_nms2_kernel<32, 6, true><<<rm.tile_base[lt.n], 256, 0, s>>>(lt, rm, thresh, nms, 1, row_count, bitmap, xend);
+    CLB_LAUNCHED();
+    compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total, bitmap);
+    CLB_LAUNCHED();
+#endif
     timer("fast").end(s);
     return CLB_OK;
 }

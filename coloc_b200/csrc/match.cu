@@ -24,11 +24,14 @@ static constexpr int MT_KEY_SHIFT = 22;             // key = dist << 22 | row-in
 static constexpr uint32_t MT_IDX_MASK = (1u << MT_KEY_SHIFT) - 1;
 static constexpr int MT_MAX_CHUNK_ROWS = 1 << MT_KEY_SHIFT;
 
-int g_match_rq = 0;      // 0 = heuristic
-int g_match_hs = 2;      // carry-save depth: 0 none(16 popc) 1 (11) 2 (8) 3 (5)
-int g_match_chunks = 0;  // 0 = heuristic
-int g_last_match_path = 0;   // 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2 (what the last launch_match used)
-extern int g_match_tc_ver;
+std::atomic<int> g_match_rq{0};      // 0 = heuristic
+std::atomic<int> g_match_chunks{0};  // 0 = heuristic
+std::atomic<int> g_last_match_path{0};   // 0 = POPC kernel, 4 = tensor-core kernel (what the last launch_match used)
+#ifdef CLB_LAB
+std::atomic<int> g_match_hs{2};      // carry-save depth: 0 none(16 popc) 1 (11) 2 (8) 3 (5)
+#else
+static constexpr int g_match_hs = 2; // the product build carries the 8-POPC tree only
+#endif
 
 // ---- PTX helpers ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -273,11 +276,12 @@ struct MatchPlan { int rq, qblocks, nchunks, rpc; };
 
 static MatchPlan plan_match(int nQ, int nT, int sm_count) {
     MatchPlan p;
-    p.rq = g_match_rq ? g_match_rq : (nQ >= 2048 ? 4 : (nQ >= 512 ? 2 : 1));
+    const int rq_knob = g_match_rq, chunks_knob = g_match_chunks;
+    p.rq = rq_knob ? rq_knob : (nQ >= 2048 ? 4 : (nQ >= 512 ? 2 : 1));
     p.qblocks = (nQ + MT_THREADS * p.rq - 1) / (MT_THREADS * p.rq);
     const int per_sm = p.rq >= 4 ? 2 : 3;
     const int target = sm_count * per_sm * 3;                       // ~3 waves of resident CTAs
-    int nchunks = g_match_chunks ? g_match_chunks : (target + p.qblocks - 1) / p.qblocks;
+    int nchunks = chunks_knob ? chunks_knob : (target + p.qblocks - 1) / p.qblocks;
     const int max_chunks = (nT + 4 * MT_TILE_ROWS - 1) / (4 * MT_TILE_ROWS);   // >= 256 rows per chunk
     if (nchunks > max_chunks) nchunks = max_chunks;
     const int min_chunks = (nT + MT_MAX_CHUNK_ROWS - 1) / MT_MAX_CHUNK_ROWS;
@@ -302,9 +306,11 @@ size_t match_scratch_bytes(int nQ, int nT) {
 template <int RQ>
 static void launch_rq(int hs, dim3 grid, cudaStream_t s, const uint4* Q, int nQ, const uint4* T, int nT, int rpc, uint2* part) {
     switch (hs) {
+#ifdef CLB_LAB
         case 0: match_kernel<RQ, 0><<<grid, MT_THREADS, 0, s>>>(Q, nQ, T, nT, rpc, part); break;
         case 1: match_kernel<RQ, 1><<<grid, MT_THREADS, 0, s>>>(Q, nQ, T, nT, rpc, part); break;
         case 3: match_kernel<RQ, 3><<<grid, MT_THREADS, 0, s>>>(Q, nQ, T, nT, rpc, part); break;
+#endif
         default: match_kernel<RQ, 2><<<grid, MT_THREADS, 0, s>>>(Q, nQ, T, nT, rpc, part); break;
     }
 }
@@ -322,7 +328,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
         if ((size_t)nchunks * nQ * sizeof(uint2) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "match scratch too small"); return CLB_EINVAL; }
         if (nchunks > 65535) { snprintf(g_err, sizeof(g_err), "too many DB chunks"); return CLB_EINVAL; }
         uint2* part = reinterpret_cast<uint2*>(scratch);
-        g_last_match_path = (g_match_tc_ver == 4 || Qx) ? g_match_tc_ver : 2;
+        g_last_match_path = (tc_version() == 4 || Qx) ? tc_version() : 2;
         int rc = launch_match_tc_kernel(dQ, Qx, nQ, Tx, nT, qblocks, nchunks, tpc, part, s);
         if (rc) return rc;
         timer("merge").begin(s);

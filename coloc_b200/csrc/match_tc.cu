@@ -27,10 +27,14 @@
 
 namespace clb {
 
-int g_match_tc = -1;        // -1 auto, 0 never, 1 always (clb_set_param "match_tc")
-int g_match_tc_chunks = 0;  // 0 = heuristic
-int g_match_tc_dbg = 0;     // timing experiments (v1 kernel): 1 no TMEM reads, 2 TMEM reads only, 3 no MMAs
-int g_match_tc_ver = 4;     // 1 / 2 = E4M3 operands, queries in smem / TMEM; 3 / 4 = E2M1 operands (kind::mxf4), queries in smem / TMEM
+std::atomic<int> g_match_tc{-1};        // -1 auto, 0 never, 1 always (clb_set_param "match_tc")
+std::atomic<int> g_match_tc_chunks{0};  // 0 = heuristic
+#ifdef CLB_LAB      // the lab build (make lab) keeps the superseded kernel generations and the timing modes for A/B
+std::atomic<int> g_match_tc_dbg{0};     // timing experiments: 1 no TMEM reads, 2 TMEM reads only, 3 no MMAs, ... (see tc4_cta)
+std::atomic<int> g_match_tc_ver{4};     // 1 / 2 = E4M3 operands, queries in smem / TMEM; 3 / 4 = E2M1 operands (kind::mxf4), queries in smem / TMEM
+#else
+static constexpr int g_match_tc_ver = 4;   // the product build carries the v4 kernel only
+#endif
 
 static constexpr int TC_TILE = 128;                      // rows per operand tile (UMMA M and N)
 static constexpr int TC_KB = 4;                          // K-blocks of 128 B per row (512 E4M3)
@@ -140,6 +144,9 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float (&v)[32]) {
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ float tc_max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+
+#ifdef CLB_LAB
 // ---- operand expansion ------------------------------------------------------------------------
 // 4 descriptor bits -> 4 E4M3 bytes: bit 1 -> 0x38 (+1.0), bit 0 -> 0xB8 (-1.0)
 __device__ __forceinline__ uint32_t tc_nib(uint32_t x) {
@@ -170,7 +177,6 @@ struct TcState { uint32_t best, second; float thr; };
 
 // 32 accumulator columns (DB rows row0 .. row0+31 of the chunk) for this thread's query, in two groups of 16:
 // a group costs 8 three-input max ops + 1 compare + 1 branch unless one of its distances beats the current second best
-__device__ __forceinline__ float tc_max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0, TcState& st) {
 #pragma unroll
     for (int g = 0; g < 2; ++g) {
@@ -202,6 +208,8 @@ __device__ __forceinline__ void tc_process32(const float (&v)[32], uint32_t row0
         }
     }
 }
+
+#endif   // CLB_LAB (v1-v3 expansion and packed-key epilogue state)
 
 // v4 epilogue state in the accumulator's own domain: the two largest dot products seen (= the two smallest distances,
 // d = (512 - x) / 2) and the row of the largest.  No conversion and no key packing inside the sweep: an update is
@@ -245,6 +253,7 @@ __device__ __forceinline__ uint2 tc_statef_keys(const TcStateF& st) {
     return make_uint2(kb, ks);
 }
 
+#ifdef CLB_LAB
 // One 128-column accumulator tile: four 32-column TMEM loads, the next one in flight while the
 // current one is scanned; the buffer is handed back to the MMA warp as soon as the last load landed.
 template <bool MASKED>
@@ -441,6 +450,7 @@ match_tc_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restric
 // DB ring (14 K-block stages, 224 KB in flight per SM).  The two 128-column accumulators (columns 256-511)
 // alternate: while the epilogue warps of query tile 0 scan D0, the MMA warp fills D1 from the same DB
 // tile, so there is no second buffer per tile and none is needed.
+#endif   // CLB_LAB (v1 kernel)
 static constexpr int TC2_STAGES = 14;
 static constexpr int TC2_SMEM_B = TC2_STAGES * TC_KB_BYTES;          // 229376
 static constexpr int TC2_SMEM_BAR = 512;
@@ -464,7 +474,7 @@ __device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t (&r)[32])
 }
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-
+#ifdef CLB_LAB
 __global__ void __launch_bounds__(TC_THREADS, 1)
 match_tc2_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
                  uint2* __restrict__ partial, int dbg) {
@@ -602,6 +612,8 @@ match_tc2_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restri
     }
 }
 
+#endif   // CLB_LAB (v2 kernel)
+
 // ---- v3: E2M1 (fp4) operands, kind::mxf4 block-scaled MMA at twice the fp8 rate ------------------------
 // +-1 is exact in E2M1 too (0x2 / 0xA), and kind::mxf4 multiplies K = 64 elements per instruction at 16 384 MAC/clk/SM:
 // 32 comparisons per clock per SM.  The block scales the instruction insists on are UE8M0 bytes; 0x7F = 2^0, so a TMEM
@@ -648,6 +660,7 @@ expand4_kernel(const uint32_t* __restrict__ rows, int n, size_t n_chunks16, uint
     out[i] = v;
 }
 
+#ifdef CLB_LAB
 __global__ void __launch_bounds__(TC_THREADS, 1)
 match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
                  uint2* __restrict__ partial, int dbg) {
@@ -779,6 +792,8 @@ match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restri
     }
 }
 
+#endif   // CLB_LAB (v3 kernel)
+
 // ---- v4: v3 with the query tiles in TMEM (TS mode) and 16 epilogue warps --------------------------------
 // tools/tc_dbg.py on v3: 5.4 T cmp/s, 6.1 T with the epilogue's TMEM reads disabled -- the scan of 128 distances per
 // thread per tile had become the long pole.  Here every accumulator row is shared by two threads (64 columns each),
@@ -834,9 +849,12 @@ __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0,
 // 1 450 -> see profiles/r1_ncu_summary.md cycles per DB tile against the 1 029 of a bare MMA stream); 2..17 = epilogue.
 // dbg (timing experiments, results are garbage unless 0 or 7): 1 no TMEM reads, 2 TMEM reads without the reduction,
 // 3 no MMAs, 7 normal sweep + real SM clock printed by a few CTAs.
+// LAB = false (the product instantiation) folds dbg to 0: none of the timing modes, clocks or printfs is compiled in.
+template <bool LAB>
 __device__ __forceinline__ void
 tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int qblock, int tile0, int ntiles, int chunk_rows,
-        uint2* __restrict__ partial_chunk, int dbg) {
+        uint2* __restrict__ partial_chunk, int dbg_rt) {
+    const int dbg = LAB ? dbg_rt : 0;
     extern __shared__ uint8_t tc_smem_raw[];
     const uint32_t raw = tc_smem_u32(tc_smem_raw);
     const uint32_t sB = (raw + 1023u) & ~1023u;
@@ -990,7 +1008,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         const int quarter = warp & 3, m = (e >> 2) & 1, half = e >> 3;
         const int row = quarter * 32 + lane;
         long long pc[6] = {0, 0, 0, 0, 0, 0};                    // dbg 7: phase clocks of epilogue warp 0
-        const bool prof = dbg == 7 && e == 0 && lane == 0 && qblock == 0 && tile0 == 0;
+        const bool prof = LAB && dbg == 7 && e == 0 && lane == 0 && qblock == 0 && tile0 == 0;
         if (prof) pc[0] = clock64();
         const int qi = qblock * TC_QROWS + m * TC_TILE + row;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -1072,7 +1090,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             const uint32_t sec = min(max(mine.x, o.x), min(mine.y, o.y));
             partial_chunk[qi] = make_uint2(b, sec);
         }
-        if (prof) {
+        if (LAB && prof) {
             pc[5] = clock64();
             printf("tc4 phases (cycles since the epilogue warp started): queries in TMEM %lld, first accumulator %lld, second %lld, sweep done %lld, merged %lld\n",
                    pc[1] - pc[0], pc[2] - pc[0], pc[3] - pc[0], pc[4] - pc[0], pc[5] - pc[0]);
@@ -1085,7 +1103,7 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
     }
-    if ((dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0 && qblock == 0 && tile0 == 0) {     // real SM clock while the sweep runs: cycles / globaltimer ns
+    if (LAB && (dbg == 7 || (dbg >= 10 && dbg != 20)) && tid == 0 && qblock == 0 && tile0 == 0) {     // real SM clock while the sweep runs: cycles / globaltimer ns
         unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         const long long c1 = clock64();
         printf("tc4 qblock %d: %lld cycles in %llu ns = %.0f MHz, %d tiles, %.1f cycles/tile; barriers + TMEM allocation %lld cycles\n", qblock, c1 - dbg_c0, t1 - dbg_t0,
@@ -1095,31 +1113,43 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
 
 __global__ void __launch_bounds__(TC4_THREADS, 1)
 match_tc4_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
-                 uint2* __restrict__ partial, int dbg) {
+                 uint2* __restrict__ partial) {
     const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
     const int tile0 = blockIdx.y * tiles_per_chunk;
     const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
     const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
-    tc4_cta(Q, nQ, Tx, blockIdx.x, tile0, ntiles, chunk_rows, partial + (size_t)blockIdx.y * nQ, dbg);
+    tc4_cta<false>(Q, nQ, Tx, blockIdx.x, tile0, ntiles, chunk_rows, partial + (size_t)blockIdx.y * nQ, 0);
 }
+#ifdef CLB_LAB      // the same CTA with the timing modes compiled in (clb_set_param "match_tc_dbg" != 0)
+__global__ void __launch_bounds__(TC4_THREADS, 1)
+match_tc4_lab_kernel(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, int nT, int tiles_per_chunk,
+                     uint2* __restrict__ partial, int dbg) {
+    const int total_tiles = (nT + TC_TILE - 1) / TC_TILE;
+    const int tile0 = blockIdx.y * tiles_per_chunk;
+    const int ntiles = min(tiles_per_chunk, total_tiles - tile0);
+    const int chunk_rows = min(ntiles * TC_TILE, nT - tile0 * TC_TILE);
+    tc4_cta<true>(Q, nQ, Tx, blockIdx.x, tile0, ntiles, chunk_rows, partial + (size_t)blockIdx.y * nQ, dbg);
+}
+#endif
 
 // Batched form: one CTA per job of a device-resident job list (all pairs of a pair list in one launch).
 __global__ void __launch_bounds__(TC4_THREADS, 1)
 match_tc4_jobs_kernel(const TcJob* __restrict__ jobs) {
     const TcJob j = jobs[blockIdx.x];
-    tc4_cta(j.Q, j.nQ, j.Tx, j.qblock, j.tile0, j.ntiles, j.chunk_rows, j.partial_chunk, 0);
+    tc4_cta<false>(j.Q, j.nQ, j.Tx, j.qblock, j.tile0, j.ntiles, j.chunk_rows, j.partial_chunk, 0);
 }
 
 // ---- host side --------------------------------------------------------------------------------
 bool tc_wanted(int nQ, int nT) {
-    if (g_match_tc == 0 || nQ <= 0 || nT <= 0) return false;
-    if (g_match_tc > 0) return true;
+    const int mode = g_match_tc;
+    if (mode == 0 || nQ <= 0 || nT <= 0) return false;
+    if (mode > 0) return true;
     return (long long)nQ * (long long)nT >= (1ll << 24);    // below that the expansion passes dominate
 }
 
 int tc_version() { return g_match_tc_ver; }
-size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (g_match_tc_ver >= 3 ? TC3_SMEM_A : TC_SMEM_A); }
-size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (g_match_tc_ver >= 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
+size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (tc_version() >= 3 ? TC3_SMEM_A : TC_SMEM_A); }
+size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (tc_version() >= 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
 
 int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s) {
     if (out_bytes == 0) return CLB_OK;
@@ -1127,10 +1157,12 @@ int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, 
     const size_t blocks = (chunks + 255) / 256;
     if (blocks > 0x7FFFFFFFull) { snprintf(g_err, sizeof(g_err), "descriptor set too large to expand"); return CLB_EINVAL; }
     timer("expand").begin(s);
-    if (g_match_tc_ver >= 3)
-        expand4_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
-    else
+#ifdef CLB_LAB
+    if (tc_version() < 3)
         expand_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
+    else
+#endif
+        expand4_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const uint32_t*>(d_rows), n, chunks, reinterpret_cast<uint4*>(d_out));
     timer("expand").end(s);
     CLB_LAUNCHED();
     return CLB_OK;
@@ -1154,8 +1186,9 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
     if (max_chunks < min_chunks) max_chunks = min_chunks;
     if (max_chunks < 1) max_chunks = 1;
     int best_c = min_chunks > 0 ? min_chunks : 1;
-    if (g_match_tc_chunks > 0) {
-        best_c = g_match_tc_chunks < max_chunks ? g_match_tc_chunks : max_chunks;
+    const int forced = g_match_tc_chunks;
+    if (forced > 0) {
+        best_c = forced < max_chunks ? forced : max_chunks;
         if (best_c < min_chunks) best_c = min_chunks;
     } else {
         // the busiest SM runs `waves` CTAs of tc_cta_cost_us(tpc) back to back
@@ -1175,7 +1208,7 @@ void tc_plan(int nQ, int nT, int sm_count, int* qblocks_out, int* nchunks_out, i
     *nchunks_out = total_tiles > 0 ? (total_tiles + *tpc_out - 1) / *tpc_out : 0;
 }
 
-bool tc_needs_qx() { return g_match_tc_ver == 1 || g_match_tc_ver == 3; }
+bool tc_needs_qx() { return tc_version() == 1 || tc_version() == 3; }
 
 // ---- batched pair lists: always the v4 kernel on E2M1 images, whatever match_tc_ver says -------
 size_t tc4_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * TC3_TILE_BYTES; }
@@ -1254,26 +1287,36 @@ int launch_match_tc_kernel(const uint64_t* dQ, const void* Qx, int nQ, const voi
     int dev = 0;
     CLB_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+        CLB_CUDA(cudaFuncSetAttribute(match_tc4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC4_SMEM_TOTAL));
+#ifdef CLB_LAB
         CLB_CUDA(cudaFuncSetAttribute(match_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
         CLB_CUDA(cudaFuncSetAttribute(match_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM_TOTAL));
         CLB_CUDA(cudaFuncSetAttribute(match_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC3_SMEM_TOTAL));
-        CLB_CUDA(cudaFuncSetAttribute(match_tc4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC4_SMEM_TOTAL));
+        CLB_CUDA(cudaFuncSetAttribute(match_tc4_lab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC4_SMEM_TOTAL));
+#endif
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     dim3 grid(qblocks, nchunks);
     timer("match").begin(s);
-    if (g_match_tc_ver == 4)
-        match_tc4_kernel<<<grid, TC4_THREADS, TC4_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
-                                                                 reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
-    else if (g_match_tc_ver == 3 && Qx)
+#ifdef CLB_LAB
+    const int ver = tc_version(), dbg = g_match_tc_dbg;
+    if (ver == 4 && dbg != 0)
+        match_tc4_lab_kernel<<<grid, TC4_THREADS, TC4_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
+                                                                     reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, dbg);
+    else if (ver == 3 && Qx)
         match_tc3_kernel<<<grid, TC_THREADS, TC3_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
-                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
-    else if (g_match_tc_ver == 1 && Qx)
+                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, dbg);
+    else if (ver == 1 && Qx)
         match_tc_kernel<<<grid, TC_THREADS, TC_SMEM_TOTAL, s>>>(reinterpret_cast<const uint8_t*>(Qx), nQ,
-                                                              reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
-    else
+                                                              reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, dbg);
+    else if (ver == 2 || ver == 3 || ver == 1)
         match_tc2_kernel<<<grid, TC_THREADS, TC2_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
-                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, g_match_tc_dbg);
+                                                                reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part, dbg);
+    else
+#endif
+        match_tc4_kernel<<<grid, TC4_THREADS, TC4_SMEM_TOTAL, s>>>(reinterpret_cast<const uint32_t*>(dQ), nQ,
+                                                                 reinterpret_cast<const uint8_t*>(Tx), nT, tpc, part);
+    (void)Qx;
     timer("match").end(s);
     CLB_LAUNCHED();
     return CLB_OK;

@@ -41,7 +41,6 @@ inline int clb_consume_pending(clb_matcher* m, cudaStream_t s) {
 namespace clb {
 // a (query rows, expanded training set) problem of a job list (api_fmap.cu)
 struct PairView { const uint64_t* Q; int nQ; const uint8_t* Tx; int nT; };
-extern int g_match_balance, g_last_match_balanced;
 }
 int run_views(clb_matcher* m, const clb::PairView* v, int nv, int threshold, float ratio,
               int32_t* d_match, int32_t* d_best, int32_t* d_second, clb_partial* d_part_out, long long t_base, cudaStream_t s);

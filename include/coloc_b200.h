@@ -79,6 +79,14 @@ int  clb_detector_create(const clb_detector_opts* opts, int device, clb_detector
 /* GPUDetector::freeGPUMemory  GPUDetector.hpp:144-155 */
 void clb_detector_destroy(clb_detector* d);
 
+/* per-detector parameters.  "fast_quirk" (default 1): 1 = FAST scans exactly the columns the COMPILED reference scans --
+ * on levels whose width has (w - 38) % 16 == 0 (214 = level 6 of a 640-wide frame, 1286 = level 6 of a 3840-wide one) the
+ * `1 << 32` at KFAST.h:243 evaluates to 1 on x86 and the last 32 columns of a row are dropped when the block walk of
+ * KFAST.h:451-459 / :256-262 lands on column w - 35 (data dependent, per row); 0 = the intended semantics, every column
+ * 3..w-4 (a deliberate deviation from the reference: different keypoints on those levels). */
+int  clb_detector_set_param(clb_detector* d, const char* name, int value);
+int  clb_detector_get_param(const clb_detector* d, const char* name, int* value_out);
+
 /* level geometry of GPUDetector.hpp:107-114 for a w x h frame; arrays of scale_levels entries */
 int  clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, int32_t* hs, float* fs);
 
@@ -126,6 +134,7 @@ int  clb_stream_submit(clb_stream* s, const uint8_t* gray, int w, int h, int str
 int  clb_stream_next(clb_stream* s, uint64_t* tag_out, const clb_keypoint** kps_out, const uint64_t** desc_out,
                      const clb_keypoint** d_kps_out, const uint64_t** d_desc_out, int* n_out);
 int  clb_stream_in_flight(const clb_stream* s);
+int  clb_stream_set_param(clb_stream* s, const char* name, int value);   /* clb_detector_set_param on every slot */
 
 /* ---------------------------------------------------------------- matcher ---------------- */
 /* GPUMatcher::GPUMatcher(MatcherOptions)  include/coloc/GPUMatcher.hpp:70-95 */
@@ -180,6 +189,40 @@ int  clb_match_partial_hostdb(clb_matcher* m, const uint64_t* dQ, int nQ, const 
  * test: first-min-wins across parts, global second = 2nd smallest of the union.  DEVICE pointers. */
 int  clb_merge_partials_dev(clb_matcher* m, const clb_partial* d_parts, int nparts, int nQ, int threshold,
                             int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
+/* ---------------------------------------------------------------- sharded map matching --- */
+/* GPUMatcher::setMapData (GPUMatcher.hpp:110-117) + matchSceneWithMap / matchFeaturesWithMap
+ * (:174-178, :252-271) with the map rows cut into contiguous shards, one per GPU.  Shard r of n holds rows
+ * [r*base + min(r, rem), ...) with base = nM / n, rem = nM % n (clb_sharded_range).  Every GPU sweeps its shard for all
+ * queries, the 16-byte-per-query clb_partial arrays are exchanged and merged in ascending shard order: bit-identical to the
+ * single-GPU scan (first row attaining the minimum wins across shard borders).
+ *   clb_sharded_create       ONE process drives `ndev` devices (devices == NULL: 0..ndev-1); partials reach the first device
+ *                            by peer copies over NVLink.
+ *   clb_sharded_create_rank  one process per GPU (torchrun / MPI): rank 0 calls clb_sharded_unique_id, the caller's own
+ *                            transport broadcasts the 128 bytes, every rank creates its handle; the exchange is one
+ *                            ncclAllGather per call.  NCCL is bound at run time (libnccl.so.2); CLB_EUNSUPPORTED without it. */
+typedef struct clb_sharded clb_sharded;
+int  clb_sharded_create(const clb_matcher_opts* opts, const int* devices, int ndev, clb_sharded** out);
+int  clb_sharded_unique_id(void* id128_out);
+int  clb_sharded_create_rank(const clb_matcher_opts* opts, int device, int rank, int nranks, const void* id128, clb_sharded** out);
+void clb_sharded_destroy(clb_sharded* s);
+int  clb_sharded_shards(const clb_sharded* s);
+int  clb_sharded_range(const clb_sharded* s, long long n_rows, int shard, long long* lo_out, long long* hi_out);
+/* setMapData: M = the WHOLE map (HOST); every shard uploads its own rows and keeps them resident (expanded once). */
+int  clb_sharded_set_map(clb_sharded* s, const uint64_t* M, long long nM);
+/* the map STAYS in host memory (pinned for overlap; kept alive by the caller): each match call streams every shard's rows
+ * in slices behind its sweep (clb_match_partial_hostdb). */
+int  clb_sharded_set_map_host(clb_sharded* s, const uint64_t* M, long long nM);
+/* rank mode, this rank's rows only: global rows [row_lo, row_lo + rows) of a map of n_total rows.
+ * where: 0 HOST rows -> resident, 1 DEVICE rows -> resident (copied), 2 HOST rows streamed per call. */
+int  clb_sharded_set_map_shard(clb_sharded* s, const uint64_t* rows_ptr, long long row_lo, int rows, long long n_total, int where);
+/* matchFeaturesWithMap over all shards: HOST queries in, HOST match[] (global MAP row or -1) out, blocking.  threshold < 0 ->
+ * opts.thresh.  Rank mode: collective, every rank passes the same queries and gets the same result. */
+int  clb_sharded_match_map(clb_sharded* s, const uint64_t* Q, int nQ, int threshold,
+                           int32_t* match_out, int32_t* best_d_out, int32_t* second_d_out);
+/* rank mode, DEVICE queries / outputs on this rank's device, asynchronous on `stream`: sweep -> ncclAllGather -> merge. */
+int  clb_sharded_match_map_dev(clb_sharded* s, const uint64_t* dQ, int nQ, int threshold,
+                               int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
 
 /* ---------------------------------------------------------------- device FeatureMap ------ */
 /* SURVEY 8(f)-1/2.  The reference keeps each frame's descriptors in host Regions (coloc::FeatureMap = idx ->
@@ -284,16 +327,16 @@ int  clb_microbench_pipes(int device, double* out8);
 int64_t clb_launch_count(void);
 /* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */
 int  clb_set_timing(int on);
-/* tuning knobs for experiments: "match_rq" (0,1,2,4), "match_hs" (0..3), "match_chunks" (0 = auto) for the
- * POPC kernel; "match_tc" (-1 auto: tensor-core path from 2^24 comparisons up, 0 never, 1 always),
- * "match_tc_ver" (1 queries in shared memory, 2 queries in TMEM), "match_tc_chunks" (0 = auto).
- * "match_balance" (-1 the time model chooses, 0 uniform chunks, 1 balanced job list: the (query block) strips cut into one contiguous
- * range per SM), "match_slice_rows" (first H2D slice of the streamed host-DB path).
- * Detector side, all variants produce identical bytes: "fast_var" (bit 0 queued score kernel, bit 1 fused scan + compaction +
- * orientation, bit 2 64x32 tiles, bit 3 8 CTAs per SM, bit 4 pre-test in 16-bit lanes, bit 5 tile-occupancy bitmap for the tail; default 55, 0 = first generation),
- * "latch_var" (bit 0 block-shaped gather, bit 1 schedule table in shared memory, bit 2 single gather path; default 3),
- * "latch_tex" (1 = gather through texture objects), "fast_nms" (0 = emit every corner, debug).
- * clb_get_param also answers "fast_var", "latch_var", "last_match_balanced" and "last_match_path": 0 = POPC kernel, 1 / 2 = tensor-core kernel v1 / v2. */
+/* Process-wide planning knobs (atomics; set them before the calls they should affect): "match_tc" (-1 auto: tensor-core
+ * path from 2^24 comparisons up, 0 never, 1 always), "match_tc_chunks" / "match_chunks" (0 = auto), "match_rq" (0 auto, 1, 2, 4
+ * queries per thread of the POPC kernel), "match_balance" (-1 the time model chooses, 0 uniform chunks, 1 balanced job list),
+ * "match_slice_rows" (first H2D slice of the streamed host-DB path).  clb_get_param also answers "last_match_path" (0 = POPC
+ * kernel, 4 = tensor-core kernel), "last_match_balanced" and "lab".
+ * Kernel-variant and timing knobs ("match_hs", "match_tc_ver", "match_tc_dbg", "fast_var", "fast_nms", "latch_var", "latch_tex")
+ * exist only in the lab build (make -C coloc_b200/csrc lab -> libcoloc_b200_lab.so, the same sources with -DCLB_LAB, which also
+ * carries the superseded kernel generations for A/B); the product library answers CLB_EUNSUPPORTED to them, so nothing a caller
+ * sets can change which kernels it runs.  Thresholds: the reference passes uint8_t (CUDAK2NN.cu:46); this ABI takes int and
+ * compares `second - best > threshold` in int, so values above 255 simply never match rather than wrapping. */
 int  clb_set_param(const char* name, int value);
 int  clb_get_param(const char* name, int* value_out);
 float clb_last_kernel_ms(const char* which);   /* "match", "describe", "fast", "resize", "merge" */

@@ -99,7 +99,7 @@ def pyramid(img, scale_factor=1.2, levels=8):
     return out
 
 
-def fast_scores(img, thresh=40, quirk=0):
+def fast_scores(img, thresh=40, quirk=1):
     img = np.ascontiguousarray(img, np.uint8)
     h, w = img.shape
     sc = np.zeros((h, w), np.uint8)
@@ -107,7 +107,8 @@ def fast_scores(img, thresh=40, quirk=0):
     return sc
 
 
-def fast_nms(img, thresh=40, quirk=0, cap=None):
+def fast_nms(img, thresh=40, quirk=1, cap=None):
+    """quirk=1 (default) = what the compiled reference does at the KFAST.h:243 `1 << 32` edge; 0 = every column scanned"""
     img = np.ascontiguousarray(img, np.uint8)
     h, w = img.shape
     cap = cap or (w * h // 4 + 16)
@@ -166,7 +167,7 @@ def match_2nn(Q, T, threshold):
     return m, b, s
 
 
-def detect_describe(img, scale_factor=1.2, levels=8, thresh=40, quirk=0, cap=None, want_pyramid=False):
+def detect_describe(img, scale_factor=1.2, levels=8, thresh=40, quirk=1, cap=None, want_pyramid=False):
     img = np.ascontiguousarray(img, np.uint8)
     h, w = img.shape
     cap = cap or (w * h // 8 + 16)

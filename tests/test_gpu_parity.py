@@ -32,11 +32,14 @@ def _check_match(clb, oracle, matcher, Q, T, thr):
 # ------------------------------------------------------------------ Hamming 2-NN
 @pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (3, 1), (7, 5), (33, 64), (64, 65), (255, 257), (300, 1000),
                                    (1000, 777), (2049, 4100), (5000, 5000)])
-@pytest.mark.parametrize("hs", [0, 1, 2, 3])
+@pytest.mark.parametrize("hs", [2, 0, 1, 3])
 def test_match_vs_oracle(clb, oracle, matcher, nq, nt, hs):
     if hs != 2 and nq > 1000:
         pytest.skip("knob sweep on small sizes only")
-    clb.set_param("match_hs", hs)
+    if hs != 2 and not clb.is_lab():
+        pytest.skip("carry-save depth variants exist in the lab build only (CLB_LIB=lab)")
+    if clb.is_lab():
+        clb.set_param("match_hs", hs)
     try:
         T = synth.random_descriptors(nt, 100 + nt)
         Q, _ = synth.planted_queries(T, nq, 200 + nq)
@@ -48,7 +51,8 @@ def test_match_vs_oracle(clb, oracle, matcher, nq, nt, hs):
         for thr in (40, 60, 0):
             _check_match(clb, oracle, matcher, Q, T, thr)
     finally:
-        clb.set_param("match_hs", 2)
+        if clb.is_lab():
+            clb.set_param("match_hs", 2)
 
 
 @pytest.mark.parametrize("rq", [1, 2, 4])
@@ -151,14 +155,19 @@ def tc_forced(clb):
     """force the tcgen05 kernels at every size (the default picks them from 2^24 comparisons up)"""
     clb.set_param("match_tc", 1)
     yield
-    clb.set_param("match_tc", -1); clb.set_param("match_tc_ver", 4); clb.set_param("match_tc_chunks", 0)
+    clb.set_param("match_tc", -1); clb.set_param("match_tc_chunks", 0)
+    if clb.is_lab():
+        clb.set_param("match_tc_ver", 4)
 
 
 @pytest.mark.parametrize("ver", [4, 3, 2, 1])
 @pytest.mark.parametrize("nq,nt", [(1, 1), (1, 2), (3, 1), (7, 5), (33, 64), (64, 65), (128, 128), (255, 257), (256, 129),
                                    (300, 1000), (1000, 777), (2049, 4100), (5000, 5000)])
 def test_match_tc_vs_oracle(clb, oracle, matcher, tc_forced, nq, nt, ver):
-    clb.set_param("match_tc_ver", ver)
+    if ver != 4 and not clb.is_lab():
+        pytest.skip("superseded tensor-core kernels exist in the lab build only (CLB_LIB=lab)")
+    if clb.is_lab():
+        clb.set_param("match_tc_ver", ver)
     T = synth.random_descriptors(nt, 100 + nt)
     Q, _ = synth.planted_queries(T, nq, 200 + nq)
     rng = np.random.default_rng(nq * 7 + nt)
@@ -243,39 +252,89 @@ def test_pyramid_vs_oracle(clb, oracle, w, h):
 
 
 # ------------------------------------------------------------------ FAST + NMS + angle
+FAST_VARS = [55, 23, 19, 7, 3, 1, 2, 0]     # fast_var (lab build): queued score kernel / fused tail / 64x32 tiles / 16-bit-lane pre-test / first generation
+
+
+def _fast_vars(clb):
+    return FAST_VARS if clb.is_lab() else [55]
+
+
+def _set_fast_var(clb, var):
+    if clb.is_lab():
+        clb.set_param("fast_var", var)
+
+
+# widths 38, 54, 70, 214, 1286: (w - 38) % 16 == 0, the levels on which the compiled reference's `1 << 32` (KFAST.h:243) bites
 @pytest.mark.parametrize("w,h,thr", [(640, 480, 40), (533, 400, 40), (1067, 600, 40), (257, 193, 20), (70, 50, 10),
-                                     (214, 161, 20), (9, 9, 5), (7, 7, 1), (6, 30, 5)])
-@pytest.mark.parametrize("var", [55, 23, 19, 7, 3, 1, 2, 0])     # fast_var: queued score kernel / fused tail / 64x32 tiles / 16-bit-lane pre-test / first generation
-def test_fast_vs_oracle(clb, oracle, w, h, thr, var):
+                                     (214, 161, 20), (214, 161, 40), (1286, 723, 40), (38, 30, 5), (54, 40, 8), (39, 20, 5),
+                                     (9, 9, 5), (7, 7, 1), (6, 30, 5)])
+@pytest.mark.parametrize("quirk", [1, 0])
+def test_fast_vs_oracle(clb, oracle, w, h, thr, quirk):
     img = synth.textured_frame(w, h, 3)
-    det = clb.Detector(max(w, 8), max(h, 8), maxkp=w * h // 4 + 16, thresh=thr)
-    clb.set_param("fast_var", var)
-    try:
-        got = det.fast_nms_angle(img, level_idx=2)
-    finally:
-        clb.set_param("fast_var", 55)
-    ref = oracle.fast_nms(img, thr, quirk=0)
+    det = clb.Detector(max(w, 8), max(h, 8), maxkp=w * h // 4 + 16, thresh=thr, fast_quirk=quirk)
+    ref = oracle.fast_nms(img, thr, quirk=quirk)
     for k in ref:
         k["angle"] = oracle.feature_angle(img, k["x"], k["y"]); k["scale"] = 2
-    assert len(got) == len(ref)
-    assert np.array_equal(got.view(np.uint8), ref.view(np.uint8))   # x, y, score, angle bits, scale, order
+    try:
+        for var in _fast_vars(clb):
+            _set_fast_var(clb, var)
+            got = det.fast_nms_angle(img, level_idx=2)
+            assert len(got) == len(ref), (var, len(got), len(ref))
+            assert np.array_equal(got.view(np.uint8), ref.view(np.uint8)), var   # x, y, score, angle bits, scale, order
+    finally:
+        _set_fast_var(clb, 55)
     det.close()
 
 
-@pytest.mark.parametrize("var", [55, 23, 7, 3, 0])
-def test_fast_noise_and_flat(clb, oracle, var):
+@pytest.mark.parametrize("w0,h0,k", [(640, 480, 0), (640, 480, 1), (3840, 2160, 0)])
+def test_fast_equals_compiled_reference_on_quirk_levels(clb, oracle, w0, h0, k):
+    """level 6 of the C1 / C5 frames (214 x 161, 1286 x 723): the CUDA path with fast_quirk = 1 (the default) against the
+    reference's own KFAST.h compiled unmodified (oracle/_ref), not only against the restatement; and the two semantics differ
+    there, so the test cannot pass by accident."""
+    if oracle.ref_cpu() is None:
+        pytest.skip("oracle/_ref/libcoloc_ref_cpu.so not built")
+    img = synth.config_frame(w0, h0, k)
+    lv = oracle.pyramid(img)[6]
+    assert (lv.shape[1] - 38) % 16 == 0
+    det = clb.Detector(lv.shape[1], lv.shape[0], maxkp=lv.size // 4 + 16, thresh=40)
+    got = det.fast_nms_angle(lv, level_idx=6)
+    ref = oracle.ref_kfast(lv, 40)
+    assert len(got) == len(ref) > 100
+    for f in ("x", "y", "score"):
+        assert np.array_equal(got[f], ref[f]), f
+    det.set_param("fast_quirk", 0)
+    q0 = det.fast_nms_angle(lv, level_idx=6)
+    assert len(q0) > len(got)                                    # the intended semantics keep the columns the reference drops
+    assert np.array_equal(q0.view(np.uint8)[:, :12], oracle.fast_nms(lv, 40, quirk=0).view(np.uint8)[:, :12])
+    det.close()
+
+
+def test_fast_noise_and_flat(clb, oracle):
     # uniform noise: every position passes the pre-test, ~1/3 are corners -- the shared-memory queues of the v2 kernel run full
     det = clb.Detector(640, 480, maxkp=200000, thresh=40)
     noise = np.random.default_rng(0).integers(0, 256, (480, 640), dtype=np.uint8)
-    clb.set_param("fast_var", var)
+    ref = oracle.fast_nms(noise, 40)
     try:
-        got = det.fast_nms_angle(noise)
-        ref = oracle.fast_nms(noise, 40)
-        assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
-        assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
+        for var in ([55, 23, 7, 3, 0] if clb.is_lab() else [55]):
+            _set_fast_var(clb, var)
+            got = det.fast_nms_angle(noise)
+            assert len(got) == len(ref) > 20000 and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["score"], ref["score"])
+            assert len(det.fast_nms_angle(np.full((480, 640), 128, np.uint8))) == 0
     finally:
-        clb.set_param("fast_var", 55)
+        _set_fast_var(clb, 55)
     det.close()
+    # noise on a quirk width: every 16-column block has pre-test passes, so the walk advances by 32 from column 3 and lands on
+    # w - 35 exactly when (w - 38) % 32 == 0 -- every row of a 230-wide image is truncated, none of a 214-wide one
+    for w in (230, 214):
+        noise = np.random.default_rng(w).integers(0, 256, (60, w), dtype=np.uint8)
+        det = clb.Detector(w, 60, maxkp=20000, thresh=40)
+        got = det.fast_nms_angle(noise); ref = oracle.fast_nms(noise, 40, quirk=1)
+        assert len(got) == len(ref) and np.array_equal(got["x"], ref["x"]) and np.array_equal(got["y"], ref["y"])
+        assert (got["x"].max() < w - 35) == (w == 230)
+        if oracle.ref_cpu() is not None:
+            rk = oracle.ref_kfast(noise, 40)
+            assert np.array_equal(got["x"], rk["x"]) and np.array_equal(got["y"], rk["y"]) and np.array_equal(got["score"], rk["score"])
+        det.close()
 
 
 def test_fast_threshold_zero_full_queues(clb, oracle):
@@ -333,11 +392,26 @@ def test_detect_describe_end_to_end(clb, oracle, w, h):
     det = clb.Detector(w, h, maxkp=100000)
     for img in (a, b):
         kps, desc = det.detect_and_describe(img)
-        okps, odesc = oracle.detect_describe(img, cap=100000)
+        okps, odesc = oracle.detect_describe(img, cap=100000)          # quirk = 1: the compiled reference's keypoint set
         assert len(kps) == len(okps) > 1000
         assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8))
         assert np.array_equal(desc, odesc)
     det.close()
+
+
+def test_config1_frame_equals_reference_semantics(clb, oracle):
+    """BASELINE config 1 frame (640x480, level 6 is 214 wide): 5 207 keypoints with the reference's column walk (the default),
+    5 232 with every column scanned; both bit-exact against the oracle, keypoints and descriptors"""
+    img = synth.config_frame(640, 480, 0)
+    counts = {}
+    for quirk in (1, 0):
+        det = clb.Detector(640, 480, maxkp=50000, fast_quirk=quirk)
+        kps, desc = det.detect_and_describe(img)
+        okps, odesc = oracle.detect_describe(img, quirk=quirk, cap=50000)
+        assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc, odesc)
+        counts[quirk] = len(kps)
+        det.close()
+    assert counts == {1: 5207, 0: 5232}, counts
 
 
 def test_config5_frame_end_to_end(clb, oracle):
@@ -347,10 +421,15 @@ def test_config5_frame_end_to_end(clb, oracle):
     img = synth.config_frame(w, h, 0)
     det = clb.Detector(w, h, maxkp=200000)
     kps, desc = det.detect_and_describe(img)
-    okps, odesc = oracle.detect_describe(img, cap=200000)
-    assert len(kps) == len(okps) > 30000
+    okps, odesc = oracle.detect_describe(img, cap=200000)              # quirk = 1 (level 6 is 1286 wide)
+    assert len(kps) == len(okps) == 50009
     assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8))
     assert np.array_equal(desc, odesc)
+    det.set_param("fast_quirk", 0)
+    k0, d0 = det.detect_and_describe(img)
+    ok0, od0 = oracle.detect_describe(img, quirk=0, cap=200000)
+    assert len(k0) == len(ok0) == 50108 and np.array_equal(k0.view(np.uint8), ok0.view(np.uint8)) and np.array_equal(d0, od0)
+    det.set_param("fast_quirk", 1)
     # a mostly flat frame with a few textured islands: nearly every row takes the sparse path
     flat = np.full((h, w), 90, np.uint8)
     for (y0, x0) in ((100, 64), (900, 2050), (1500, 3700), (2100, 0), (40, 3776)):

@@ -96,7 +96,9 @@ def test_fast_matches_reference(ref_cpu, w, h, seed, thr):
 @pytest.mark.parametrize("w", [70, 102, 214, 1286])
 def test_fast_shift_ub_edge(ref_cpu, w):
     """KFAST.h:243 `1 << 32`: x86 drops the last 32 columns on affected rows.  quirk=1 reproduces the
-    compiled reference exactly; quirk=0 (intended semantics, what the CUDA path implements) is a superset."""
+    compiled reference exactly (and is what the CUDA path runs by default, fast_quirk = 1); quirk=0 is the intended
+    semantics.  The SCORE maps nest (quirk 1 = quirk 0 with some row tails zeroed); the keypoint sets after NMS do not:
+    a score dropped in the last 32 columns un-suppresses its neighbours."""
     O = ref_cpu
     img = synth.textured_frame(w, 120, 7)
     ref = O.ref_kfast(img, 20)
