@@ -305,7 +305,8 @@ def test_fast_equals_compiled_reference_on_quirk_levels(clb, oracle, w0, h0, k):
     det.set_param("fast_quirk", 0)
     q0 = det.fast_nms_angle(lv, level_idx=6)
     assert len(q0) > len(got)                                    # the intended semantics keep the columns the reference drops
-    assert np.array_equal(q0.view(np.uint8)[:, :12], oracle.fast_nms(lv, 40, quirk=0).view(np.uint8)[:, :12])
+    o0 = oracle.fast_nms(lv, 40, quirk=0)
+    assert len(q0) == len(o0) and all(np.array_equal(q0[f], o0[f]) for f in ("x", "y", "score"))
     det.close()
 
 
