@@ -180,11 +180,12 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
-def c2_extra(clb, torch, synth):
-    """config 2 (1280x720 pair, 8 levels): detect+describe per frame and the pair match, device-timed."""
-    w, h = 1280, 720
+def frame_extra(clb, torch, synth, w=1280, h=720):
+    """one BASELINE frame (config 2: 1280x720, config 5: 3840x2160; 8 levels): detect+describe stage by stage, device-timed, with
+    each stage's algorithmic bytes against the measured HBM peak, plus the blocking per-frame call and, for
+    config 2, the pair match."""
     a, b, _ = synth.config_frame_pair(w, h, 0)
-    det = clb.Detector(w, h, maxkp=120000)
+    det = clb.Detector(w, h, maxkp=400000 if w * h > 2000000 else 120000)
     clb.set_timing(True)
     res = {}
     pin = torch.empty((h, w), dtype=torch.uint8).pin_memory(); pin.numpy()[:] = a
@@ -201,32 +202,37 @@ def c2_extra(clb, torch, synth):
     e2e_ms = 1e3 * float(np.median(ts))
     ws, hs, _ = det.level_dims(w, h)
     pyr_bytes = sum(x * y for x, y in zip(ws, hs))
+    hbm = measured_peaks().get("hbm_gbs") or 6558.4
     res["frame"] = f"{w}x{h}, 8 levels x1.2, FAST thresh 40"
     res["keypoints"] = int(n)
     res["stage_ms"] = st
     res["detect_describe_e2e_ms"] = e2e_ms
     res["frames_per_s_e2e"] = 1e3 / e2e_ms
     res["frames_per_s_kernels"] = 1e3 / max(1e-9, sum(st.values()))
-    res["algorithmic_GBps"] = {"resize": pyr_bytes / st["resize"] / 1e6 if st["resize"] else None,
-                               "fast": (pyr_bytes + 20 * n) / st["fast"] / 1e6 if st["fast"] else None,
-                               "describe": 4180 * n / st["describe"] / 1e6 if st["describe"] else None}
-    ka, da = ka.copy(), da.copy()
-    kb, db = det.detect_and_describe(b)
-    m = clb.Matcher(maxkp=len(da) + len(db) + 16)
-    for it in range(3):
-        m.compute_matches(da, db, 40)
-    res["pair_match_ms"] = clb.last_kernel_ms("match") + clb.last_kernel_ms("merge")
-    res["pair_match_cmp_per_s"] = len(da) * len(db) / (res["pair_match_ms"] * 1e-3)
+    gb = {"resize": pyr_bytes / st["resize"] / 1e6 if st["resize"] else None,
+          "fast": (pyr_bytes + 20 * n) / st["fast"] / 1e6 if st["fast"] else None,
+          "describe": 4180 * n / st["describe"] / 1e6 if st["describe"] else None}
+    res["algorithmic_GBps"] = gb
+    res["hbm_frac"] = {k: (v / hbm if v else None) for k, v in gb.items()}
+    res["hbm_peak_GBps"] = hbm
+    if w == 1280:
+        ka, da = ka.copy(), da.copy()
+        kb, db = det.detect_and_describe(b)
+        m = clb.Matcher(maxkp=len(da) + len(db) + 16)
+        for it in range(3):
+            m.compute_matches(da, db, 40)
+        res["pair_match_ms"] = clb.last_kernel_ms("match") + clb.last_kernel_ms("merge")
+        res["pair_match_cmp_per_s"] = len(da) * len(db) / (res["pair_match_ms"] * 1e-3)
+        m.close()
     clb.set_timing(False)
-    det.close(); m.close()
+    det.close()
     return res
 
 
-def c2_cpu_baseline(O, synth):
-    """cpu_baseline leg for config 2: the same 1280x720 frame through the CPU path of BASELINE.md section 3 on the
+def detect_cpu_baseline(O, synth, w=1280, h=720):
+    """cpu_baseline leg for config 2 / config 5: the same frame through the CPU path of BASELINE.md section 3 on the
     box's host cores -- resize + LATCH are the oracle restatements (OpenMP; the reference has no CPU LATCH), FAST+NMS is
     the reference's own KFAST<true,true> (std::async bands) when oracle/_ref is built, orientation is the restatement."""
-    w, h = 1280, 720
     a = synth.config_frame(w, h, 0)
     have_ref = O.ref_cpu() is not None
     best = None
@@ -244,7 +250,7 @@ def c2_cpu_baseline(O, synth):
         if best is None or tot < best[0]:
             best = (tot, st, len(kps))
     tot, st, n = best
-    return {"frame": "1280x720, 8 levels x1.2, FAST thresh 40", "keypoints": int(n), "frames_per_s": 1.0 / tot,
+    return {"frame": f"{w}x{h}, 8 levels x1.2, FAST thresh 40", "keypoints": int(n), "frames_per_s": 1.0 / tot,
             "stage_ms": {k: 1e3 * v for k, v in st.items()}, "cores": os.cpu_count(),
             "kind": {"resize": "port", "fast_nms": "reference" if have_ref else "port", "describe": "port"},
             "note": "fast_nms excludes the orientation pass when the reference KFAST is timed (featureAngle is <2 % of it)"}
@@ -288,61 +294,140 @@ def residuals_extra(clb, torch, O):
     return out
 
 
-def stream_extra(clb, torch, synth, w, h, nframes, with_match, distinct=4):
-    """throughput mode (clb_stream_*): `nframes` frames of w x h from pinned host memory, up to 3 in flight; per frame the
-    keypoints + descriptors come back to pinned host memory and, with_match, frame k is matched against frame k-1 on the
-    device (descriptors never leave it) and the match list is read back.  Wall-clock frames/s, everything included."""
+def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, world=1, dev=None, distinct=4):
+    """throughput mode (clb_stream_*): `nframes` frames of w x h from pinned host memory dealt ROUND-ROBIN over the ranks (frame k
+    goes to rank k % world; replicas, no exchange inside a frame -- SURVEY 8e), up to 3 in flight per GPU; per frame the
+    keypoints + descriptors come back to pinned host memory and, with_match, each rank matches consecutive frames of its
+    sub-stream on the device (descriptors never leave it) and reads the match list back.  At the end ONE NCCL gather moves the
+    per-frame (keypoint count, match count) table and the match lists to rank 0.  Wall clock from a common barrier to the
+    slowest rank's last result, everything included; frames/s = nframes / that."""
     pins = []
     views, _ = synth.config_views(w, h, distinct)            # consecutive frames see the same scene (matches exist)
     for i in range(distinct):
         t = torch.empty((h, w), dtype=torch.uint8).pin_memory(); t.numpy()[:] = views[i]; pins.append(t)
     maxkp = 400000 if w * h > 2000000 else 120000
-    fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp)
+    row = 65536 if w * h > 2000000 else 32768                # gathered match-list row (lists longer than this are cut in the gather only)
+    devi = dev.index if dev is not None else 0
+    fs = clb.FrameStream(w, h, depth=5, maxkp=maxkp, device=devi)
     INFLIGHT = int(os.environ.get("CLB_STREAM_INFLIGHT", "3"))
-    m = clb.Matcher(maxkp=maxkp) if with_match else None
-    # match lists are read back one frame late (two device + two pinned host buffers): the host never waits on the sweep it
-    # has just queued, as a consumer that pipelines its geometric stage would not
-    outs = [torch.zeros(maxkp, dtype=torch.int32, device="cuda") for _ in range(2)] if with_match else None
+    m = clb.Matcher(maxkp=maxkp, device=devi) if with_match else None
+    mine = list(range(rank, nframes, world))
+    nloc = (nframes + world - 1) // world
+    # match lists are read back one frame late (two pinned host buffers): the host never waits on the sweep it has just
+    # queued, as a consumer that pipelines its geometric stage would not
+    lists = torch.full((nloc, row), -2, dtype=torch.int32, device=dev) if with_match else None
+    outs = [torch.zeros(maxkp, dtype=torch.int32, device=dev) for _ in range(2)] if with_match else None
     houts = [torch.zeros(maxkp, dtype=torch.int32).pin_memory() for _ in range(2)] if with_match else None
     evs = [torch.cuda.Event() for _ in range(2)] if with_match else None
+    table = torch.zeros((nloc, 2), dtype=torch.int32)
     st = torch.cuda.current_stream().cuda_stream
-    res = {}
 
-    def run(n):
+    def run(frames, record):
+        n = len(frames)
         sub = done = 0; nk = 0; ncmp = 0; nm = 0
         prev = None
-        pending = None                      # (buffer index, rows) of the match list still in flight
+        pending = None                      # (buffer index, rows, local frame) of the match list still in flight
         while done < n:
             while sub < n and fs.in_flight() < INFLIGHT:
-                fs.submit(pins[sub % distinct].numpy(), tag=sub); sub += 1
+                fs.submit(pins[frames[sub] % distinct].numpy(), tag=sub); sub += 1
             tag, k, d, dk, dd, cnt = fs.next(copy=False)
             nk += cnt
+            if record:
+                table[done, 0] = cnt
             if with_match and prev is not None and cnt > 0 and prev[1] > 0:
                 b = done & 1
                 m.match_dev(dd, cnt, prev[0], prev[1], 40, outs[b], stream=st)
                 houts[b][:cnt].copy_(outs[b][:cnt], non_blocking=True); evs[b].record()
+                if record:
+                    lists[done, :min(cnt, row)].copy_(outs[b][:min(cnt, row)], non_blocking=True)
                 ncmp += cnt * prev[1]
                 if pending is not None:
-                    evs[pending[0]].synchronize(); nm += int((houts[pending[0]][:pending[1]] >= 0).sum())
-                pending = (b, cnt)
+                    evs[pending[0]].synchronize(); c = int((houts[pending[0]][:pending[1]] >= 0).sum()); nm += c
+                    if record:
+                        table[pending[2], 1] = c
+                pending = (b, cnt, done)
             prev = (dd, cnt)
             done += 1
         if pending is not None:
-            evs[pending[0]].synchronize(); nm += int((houts[pending[0]][:pending[1]] >= 0).sum())
+            evs[pending[0]].synchronize(); c = int((houts[pending[0]][:pending[1]] >= 0).sum()); nm += c
+            if record:
+                table[pending[2], 1] = c
         return nk, ncmp, nm
 
-    run(min(8, nframes))
+    run(mine[:min(8, len(mine))], False)
     torch.cuda.synchronize()
-    t0 = time.perf_counter(); nk, ncmp, nm = run(nframes); torch.cuda.synchronize(); dt = time.perf_counter() - t0
-    res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": INFLIGHT, "keypoints_per_frame": nk / nframes,
-           "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt,
-           "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0)}
+    if world > 1:                                        # NCCL sets its send / recv channels up on first use: not part of a frame stream
+        wt = torch.zeros(8, dtype=torch.int32, device=dev)
+        dist.gather(wt, [torch.empty_like(wt) for _ in range(world)] if rank == 0 else None, dst=0)
+        torch.cuda.synchronize()
+        dist.barrier()
+    t0 = time.perf_counter()
+    nk, ncmp, nm = run(mine, True)
+    torch.cuda.synchronize()
+    gathered = None
+    if world > 1:                                        # the one exchange: per-frame counts (+ match lists) to rank 0
+        tab_d = table.to(dev)
+        gt = [torch.empty_like(tab_d) for _ in range(world)] if rank == 0 else None
+        dist.gather(tab_d, gt, dst=0)
+        if with_match:
+            gl = [torch.empty_like(lists) for _ in range(world)] if rank == 0 else None
+            dist.gather(lists, gl, dst=0)
+        torch.cuda.synchronize()
+        if rank == 0:
+            gathered = torch.stack(gt).cpu().numpy()
+    dt = time.perf_counter() - t0
+    tm = torch.tensor([dt, float(nk), float(ncmp), float(nm)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = tm.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tm, op=dist.ReduceOp.SUM)
+        dt = float(mx[0].item())
+    nk, ncmp, nm = float(tm[1].item()), float(tm[2].item()), float(tm[3].item())
+    res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": INFLIGHT, "ranks": world, "keypoints_per_frame": nk / nframes,
+           "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt, "wall_ms": dt * 1e3,
+           "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0),
+           "dealing": "frame k -> rank k % world; each rank matches consecutive frames of its own sub-stream",
+           "exchange": ("one NCCL gather of the per-frame (keypoints, matches) table" + (" and the match lists" if with_match else "") + " to rank 0") if world > 1 else "none"}
+    if gathered is not None:
+        res["gathered_keypoints"] = int(gathered[:, :, 0].sum())
     if with_match:
-        res["match_cmp_per_s"] = ncmp / dt; res["matches_per_frame"] = nm / max(1, nframes - 1)
+        res["match_cmp_per_s"] = ncmp / dt; res["matches_per_frame"] = nm / max(1, nframes - world)
     fs.close()
     if m:
         m.close()
     return res
+
+
+def reference_kernels_extra(clb, torch, O, synth):
+    """the reference's own CUDA kernels (src/CLATCH.cu, src/CUDAK2NN.cu compiled unmodified for sm_100a into oracle/_ref by
+    oracle/Makefile -- the kernels this library replaces) timed on this B200 on the config-2 frame pair, next to ours on the
+    same input.  Checker library, N = 1 only; nothing of it is on the product path."""
+    if O.ref_gpu() is None:
+        return {"unavailable": "oracle/_ref/libcoloc_ref_gpu.so not built"}
+    w, h = 1280, 720
+    a, b, _ = synth.config_frame_pair(w, h, 0)
+    det = clb.Detector(w, h, maxkp=120000)
+    ka, da = det.detect_and_describe(a); ka, da = ka.copy(), da.copy()
+    kb, db = det.detect_and_describe(b); kb, db = kb.copy(), db.copy()
+    pyr = det.pyramid(a)
+    clb.set_timing(True)
+    for _ in range(3):
+        det.detect_and_describe(a)
+    ours_latch = clb.last_kernel_ms("describe")
+    m = clb.Matcher(maxkp=len(da) + len(db) + 16)
+    for _ in range(3):
+        mm = m.compute_matches(da, db, 40)
+    ours_match = clb.last_kernel_ms("match") + clb.last_kernel_ms("merge")
+    clb.set_timing(False)
+    rdesc, ref_latch = O.ref_gpu_latch(pyr, ka, iters=5)
+    rm, ref_match = O.ref_gpu_k2nn(da, db, 40, iters=5)
+    det.close(); m.close()
+    cmp_ = float(len(da)) * len(db)
+    return {"frame_pair": f"{w}x{h}, {len(ka)} / {len(kb)} keypoints",
+            "CLATCH_kernel_ms": ref_latch, "latch_kernel_ms": ours_latch, "latch_speedup": ref_latch / ours_latch if ours_latch else None,
+            "latch_same_descriptors": bool(np.array_equal(rdesc, da)),
+            "CUDAK2NN_kernel_ms": ref_match, "match_kernels_ms": ours_match, "match_speedup": ref_match / ours_match if ours_match else None,
+            "CUDAK2NN_cmp_per_s": cmp_ / (ref_match * 1e-3), "match_cmp_per_s": cmp_ / (ours_match * 1e-3),
+            "match_same_list": bool(np.array_equal(rm, mm))}
 
 
 def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
@@ -453,13 +538,17 @@ def run_ours(args, rank, world, local_rank):
     Qn, src = make_queries(NQ, NT)
     Q_host = torch.from_numpy(Qn.view(np.int64)).pin_memory()
     dT = T_host.to(dev); dQ = Q_host.to(dev)
-    matcher = clb.Matcher(maxkp=max(hi - lo, NQ) + 16, device=local_rank)
-    sm = shard.ShardedMatcher(matcher)
-    sm.set_shard_dev(dT, lo)
+    # The sharded matcher of the C ABI (clb_sharded_*, rank mode): this rank's DB rows resident, per step a local sweep,
+    # ONE ncclAllGather of nQ x 16 B per rank inside the library, merge.  torch.distributed only carries the 128-byte NCCL id.
+    uid = [clb.ShardedMatcher.unique_id() if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(uid, src=0)
+    sm = clb.ShardedMatcher(device=local_rank, rank=rank, nranks=world, uid=uid[0], thresh=THRESH, maxkp=max(hi - lo, NQ) + 16)
+    assert sm.shard_range(NT, rank) == (lo, hi)
+    sm.set_map_shard(dT, lo, NT, where=1)                 # GPUMatcher::setMapData analogue: once per map, expanded once
     out = torch.zeros((3, NQ), dtype=torch.int32, device=dev)
-    parts = torch.empty((NQ, 4), dtype=torch.int32, device=dev)
-    gath = torch.empty((world, NQ, 4), dtype=torch.int32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+    st = torch.cuda.current_stream().cuda_stream
 
     def barrier():
         if world > 1:
@@ -467,23 +556,11 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
 
     def step_resident():
-        sm.match_dev(dQ, NQ, THRESH, out, parts, gath)
+        sm.match_map_dev(dQ, NQ, THRESH, out[0], out[1], out[2], stream=st)
 
-    def step_e2e():
-        # the user-facing path with HOST buffers: this rank's DB rows are streamed from pinned host memory in slices behind the
-        # sweep (clb_match_partial_hostdb), queries H2D, [all-gather of partials], merge, D2H of match[]
-        st = torch.cuda.current_stream().cuda_stream
-        q = Q_host.to(dev, non_blocking=True)
-        matcher.match_partial_hostdb(q, NQ, T_host, hi - lo, lo, parts, stream=st)
-        if world > 1:
-            dist.all_gather_into_tensor(gath.view(-1), parts.view(-1))
-            matcher.merge_partials_dev(gath, world, NQ, THRESH, out[0], out[1], out[2], stream=st)
-        else:
-            matcher.merge_partials_dev(parts, 1, NQ, THRESH, out[0], out[1], out[2], stream=st)
-        return out[0].cpu()
-
-    # pipe roofline denominator, measured now on this GPU (MEASURED_PEAKS.json has no POPC figure)
+    # roofline denominators measured now on this GPU (MEASURED_PEAKS.json has neither a POPC nor an fp4 figure)
     pipes = clb.microbench_pipes(local_rank)
+    mma = clb.microbench_mma(local_rank) if rank == 0 else None
 
     for _ in range(max(3, args.warmup)):
         step_resident()
@@ -504,23 +581,40 @@ def run_ours(args, rank, world, local_rank):
     clb.set_timing(False)
     my_ms = sum(a.elapsed_time(b) for a, b in ev)
 
-    # correctness guard inside the bench (not timed): planted matches recovered
-    match = out[0].cpu().numpy()
+    # correctness guards inside the bench (not timed): planted matches recovered, and a 64-query slice of the SHARDED result
+    # against the oracle's scan of the whole 2 M-row DB (rank 0 builds the full DB for it)
+    res = out.cpu().numpy()
+    match = res[0]
     t = src >= 0
     recovered = float((match[t] == src[t]).mean())
+    oracle_slice = None
+    if rank == 0:
+        import oracle as O
+        T_full = T_host.numpy().view(np.uint64) if world == 1 else make_db_shard(0, NT)
+        sl = slice(1000, 1064)
+        ro = O.match_2nn(Qn[sl], T_full, THRESH)
+        oracle_slice = bool(all(np.array_equal(res[k][sl], ro[k]) for k in range(3)))
+        del T_full
 
-    # e2e
+    # e2e: the user-facing host-buffer call.  The map rows stay in pinned HOST memory and are streamed in slices behind the
+    # sweep on every call (clb_sharded_set_map_shard where = 2 -> clb_match_partial_hostdb); clb_sharded_match_map copies the
+    # queries H2D, sweeps, all-gathers, merges, copies match[] D2H and returns after a stream sync.
+    sm.set_map_shard(T_host, lo, NT, where=2)
+    match_host = torch.zeros(NQ, dtype=torch.int32).pin_memory()
+    mh = match_host.numpy()
+
+    def step_e2e():
+        sm.match_map(Q_host, THRESH, out=mh)
+
     for _ in range(2):
         step_e2e()
     barrier()
     t0 = time.perf_counter()
-    e_ev0 = torch.cuda.Event(enable_timing=True); e_ev1 = torch.cuda.Event(enable_timing=True)
-    e_ev0.record()
     for _ in range(args.steps):
-        step_e2e()
-    e_ev1.record(); torch.cuda.synchronize()
-    my_e2e_ms = e_ev0.elapsed_time(e_ev1)
-    e2e_same = bool(np.array_equal(step_e2e().numpy(), match))      # not timed: the streamed path returns the resident path's list
+        step_e2e()                                     # blocking: every call ends with its own stream sync
+    torch.cuda.synchronize()
+    my_e2e_ms = (time.perf_counter() - t0) * 1e3
+    e2e_same = bool(np.array_equal(mh, match))         # the streamed path returns the resident path's list
     clocks = sampler.stop()                            # sampled across both timed regions (device-resident and e2e)
     barrier()
 
@@ -528,19 +622,34 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
     tot_ms, e2e_ms = tm.tolist()
+    sm.close()
+    del dT, flush
     c3 = c3_extra(clb, torch, dist, synth, shard, rank, world, dev)      # collective: every rank takes part
+    streams = {}
+    for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
+                   ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
+        ok = 1
+        try:
+            streams[key] = stream_extra(clb, torch, dist, synth, *a, rank=rank, world=world, dev=dev)
+        except Exception as e:
+            ok = 0; streams[key + "_error"] = repr(e)
+        if world > 1:                                   # a rank that failed must not leave the others inside a collective
+            fl = torch.tensor([ok], dtype=torch.int32, device=dev); dist.all_reduce(fl, op=dist.ReduceOp.MIN)
+            if int(fl.item()) == 0:
+                break
     if rank != 0:
         return
     cmp_per_step = float(NQ) * float(NT)
     value = cmp_per_step * args.steps / (tot_ms * 1e-3)
     e2e = cmp_per_step * args.steps / (e2e_ms * 1e-3)
     # roofline of the dominant kernel.  Algorithmic unit: 16 POPC32 per 512-bit comparison; the
-    # tensor-core kernel does the same comparison as a K=512 +-1 E4M3 dot product = 1024 flop.
+    # tensor-core kernel does the same comparison as a K=512 +-1 dot product = 1024 flop.
     k_ms = float(np.mean(kernel_ms))
     path = clb.get_param("last_match_path")
     cmp_s_kernel = float(NQ) * (hi - lo) / (k_ms * 1e-3)
     popc_ach = 16.0 * cmp_s_kernel / 1e9                        # G POPC32/s equivalent
     popc_frac = popc_ach / pipes["popc_gops"]
+    alg_bytes = 64 * (NQ + (hi - lo)) + 4 * NQ                  # 64 (nQ + nT) + 4 nQ per call
     if path == 0:
         roof = {"bound": "popc", "achieved": popc_ach, "peak": pipes["popc_gops"], "unit": "G POPC32/s", "frac": popc_frac,
                 "traffic": None, "kernel": "clb::match_kernel<4,2>", "kernel_ms": k_ms,
@@ -550,50 +659,61 @@ def run_ours(args, rank, world, local_rank):
     else:
         peaks = measured_peaks()
         bf16 = peaks.get("bf16_tflops")
-        mult = 4.0 if path >= 3 else 2.0                       # fp4 (kind::mxf4) issues at 4x, fp8 at 2x the bf16 rate
-        # Denominator: the tensor pipe's issue rate for this kind at the GPU's max SM clock -- one M128 N128 K64 (fp4) or K32 (fp8)
-        # tcgen05.mma per 64 cycles per SM (B300_MICROARCH.md "tcgen05 floor"; a bare stream of this kernel's MMAs runs at
-        # 64.3 cycles each: tools/tc_dbg.py match_tc_dbg=10).  MEASURED_PEAKS.json only holds a bf16 cuBLAS figure taken
-        # under the 1 kW power cap at ~1.36 GHz; 4x (2x) that figure is reported beside it -- this kernel's +-1 operands
-        # draw ~400 W and run at ~1.84 GHz, so it exceeds that number.
         sm_count = int(pipes.get("sm_count", 148)); max_mhz = float(clocks.get("sm_max_mhz") or 1965.0)
-        mac_per_clk = 16384.0 if path >= 3 else 8192.0
-        peak_tf = 2.0 * mac_per_clk * sm_count * max_mhz * 1e6 / 1e12
+        nominal_tf = 2.0 * 16384.0 * sm_count * max_mhz * 1e6 / 1e12
         ach_tf = 1024.0 * cmp_s_kernel / 1e12
+        # Denominator: MEASURED in this run -- a bare stream of the sweep's own tcgen05.mma (kind::mxf4.block_scale M128 N128 K64)
+        # on every SM for ~10 ms (clb_microbench_mma), at the clock the part held under it.  The issue rate at the max SM
+        # clock (16 384 MAC/clk/SM) is kept beside it as peak_nominal.
+        peak_tf = float(mma["tflops"])
         roof = {"bound": "tensor", "achieved": ach_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach_tf / peak_tf,
-                "traffic": None, "kernel": {1: "clb::match_tc_kernel", 2: "clb::match_tc2_kernel", 3: "clb::match_tc3_kernel",
-                                            4: "clb::match_tc4_kernel"}[path], "kernel_ms": k_ms,
-                "peak_source": f"tensor-pipe issue rate: {mac_per_clk:.0f} MAC/clk/SM x {sm_count} SMs x {max_mhz:.0f} MHz (max SM clock); "
-                               "MEASURED_PEAKS.json has no fp8/fp4 figure, see vs_measured_bf16",
-                "vs_measured_bf16": {"bf16_tflops": bf16, "multiplier": mult, "frac": (ach_tf / (mult * bf16)) if bf16 else None,
-                                     "note": "bf16_tflops is cuBLAS under the 1 kW power cap (SM ~1.36 GHz); > 1 is possible for a kernel that is not power-capped"},
-                "frac_of_nominal": ach_tf / (9000.0 if path >= 3 else 4500.0),
+                "traffic": None, "kernel": "clb::match_tc4_kernel", "kernel_ms": k_ms,
+                "peak_source": "clb_microbench_mma in this run: bare tcgen05.mma kind::mxf4 stream on all SMs, CUDA events; "
+                               f"{mma['cycles_per_mma']:.1f} cycles per M128 N128 K64 MMA = {mma['mac_per_clk_sm']:.0f} MAC/clk/SM at {mma['sm_mhz']:.0f} MHz",
+                "peak_measured": mma,
+                "peak_nominal": {"tflops": nominal_tf, "frac": ach_tf / nominal_tf,
+                                 "source": f"issue rate 16384 MAC/clk/SM x {sm_count} SMs x {max_mhz:.0f} MHz (max SM clock)"},
+                "vs_measured_bf16": {"bf16_tflops": bf16, "multiplier": 4.0, "frac": (ach_tf / (4.0 * bf16)) if bf16 else None,
+                                     "note": "MEASURED_PEAKS.json bf16_tflops is cuBLAS under the 1 kW power cap (SM ~1.36 GHz); fp4 issues at 4x the bf16 rate"},
                 "popc_roofline": {"achieved": popc_ach, "peak": pipes["popc_gops"], "unit": "G POPC32/s", "frac": popc_frac,
                                   "note": "north_star's roofline: 16 POPC32 per comparison against the measured POPC pipe; "
                                           "the tensor-core formulation is what lets frac exceed 1"},
-                "note": ("hamming = (512 - <q,t>)/2 over +-1 E2M1 operands, tcgen05.mma kind::mxf4.block_scale (unit scales) M128 N128 K64, "
-                         "fp32 accumulate (exact); 1024 flop per comparison; DB expansion (64 B -> 256 B per row) is inside the step"
-                         if path >= 3 else
-                         "hamming = (512 - <q,t>)/2 over +-1 E4M3 operands, tcgen05.mma kind::f8f6f4 M128 N128 K32, fp32 accumulate "
-                         "(exact); 1024 flop per comparison; DB expansion (64 B -> 512 B per row) is inside the step"),
+                "note": "hamming = (512 - <q,t>)/2 over +-1 E2M1 operands, tcgen05.mma kind::mxf4.block_scale (unit scales) M128 N128 K64, "
+                        "fp32 accumulate (exact); 1024 flop per comparison.  `value` sweeps the RESIDENT map: its E2M1 operand image "
+                        "(64 B -> 256 B per row) was built once at set_map, as the reference's setMapData is once per map; only "
+                        "`e2e` copies and expands the rows inside every step",
                 "pipes": pipes}
     try:    # dram__bytes_read + dram__bytes_write of one launch of this kernel at this size (one `ncu --set full` capture, committed)
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_match_traffic.json")) as f:
-            tj = json.load(f)
-        if tj.get("kernel") == roof.get("kernel") and world == 1 and NQ == 50000 and NT == 2000000:
-            roof["traffic"] = tj["traffic_bytes_per_launch"]
-            roof["traffic_detail"] = {k: tj[k] for k in ("algorithmic_bytes_per_launch", "tensor_pipe_active_pct_of_active", "sm_clock_ghz", "source", "reading")}
+        for name in ("r2_match_traffic.json", "r1_match_traffic.json"):
+            fn = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", name)
+            if not os.path.exists(fn):
+                continue
+            with open(fn) as f:
+                tj = json.load(f)
+            if tj.get("kernel") == roof.get("kernel") and world == 1 and NQ == 50000 and NT == 2000000:
+                roof["traffic"] = tj["traffic_bytes_per_launch"]
+                roof["algorithmic_bytes"] = alg_bytes
+                roof["traffic_over_algorithmic"] = tj["traffic_bytes_per_launch"] / alg_bytes
+                roof["traffic_detail"] = {"source": "profiles/" + name,
+                                          "reading": "4x from the E2M1 operand image the sweep reads (256 B per DB row instead of 64 B) and 2x because a "
+                                                     "chunk's image (~171 MB) outlives the 126 MB L2 between the two query blocks that share it; at "
+                                                     "~80 GB/s it costs no time (the kernel is tensor-pipe bound) but it is 8x SURVEY 8(d)'s 131.4 MB"}
+            break
     except (OSError, ValueError, KeyError):
         pass
     line = {"metric": "hamming_512b_comparisons_per_s", "value": value, "unit": "comparisons/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": tot_ms / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": value / PUBLISHED_CMP_S,
-            "dtype": ("u32 xor/popc" if path == 0 else ("e2m1" if path >= 3 else "e4m3") + " +-1 operands, f32 accumulate (exact integers)"), "data": "synthetic",
+            "dtype": ("u32 xor/popc" if path == 0 else "e2m1 +-1 operands, f32 accumulate (exact integers)"), "data": "synthetic",
             "config": {"workload": "C4 map relocalization: 50k queries x 2M-row DB, 512-bit descriptors, 2-NN + margin test",
                        "nQ": NQ, "nT": NT, "threshold": THRESH, "parallelism": f"db-rows x{world}",
+                       "api": "clb_sharded_* (C ABI, rank mode): sweep + ncclAllGather of nQ x 16 B per rank + merge inside the library",
                        "l2": "256 MiB device fill between steps, outside the per-step event pairs",
-                       "planted_match_recall": recovered, "e2e_equals_resident": e2e_same,
-                       "e2e_path": "clb_match_partial_hostdb: DB rows streamed from pinned host memory in slices behind the sweep"},
+                       "planted_match_recall": recovered, "oracle_slice_equal": oracle_slice,
+                       "oracle_slice": "queries 1000..1063 of the sharded result (match, best, second) == oracle scan of all 2 M rows",
+                       "e2e_equals_resident": e2e_same,
+                       "e2e_path": "clb_sharded_match_map: queries H2D, DB rows streamed from pinned host memory in slices behind the sweep, "
+                                   "all-gather, merge, match[] D2H, stream sync; wall clock over K blocking calls"},
             "e2e": {"value": e2e, "unit": "comparisons/s",
                     "h2d_bytes_per_step": int(T_host.numel() * 8 + Q_host.numel() * 8), "d2h_bytes_per_step": int(NQ * 4)},
             "gpu_launches": int(launches),
@@ -601,6 +721,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roof,
             "extra": {"c3_pairs": c3},
             }
+    line["extra"].update(streams)
     if world == 1:
         # CPU baseline beside it (bounded sample) + config-2 stage numbers
         import oracle as O
@@ -618,22 +739,16 @@ def run_ours(args, rank, world, local_rank):
         line["cpu_baseline"] = {"value": nq_s * float(NT) / dt, "unit": "comparisons/s", "cores": os.cpu_count(), "kind": kind,
                                 "sample": f"{nq_s} of {NQ} queries x {NT} DB rows, one pass ({dt:.1f} s)"}
         try:
-            line["cpu_baseline"]["c2_detect_describe"] = c2_cpu_baseline(O, synth)
+            line["cpu_baseline"]["c2_detect_describe"] = detect_cpu_baseline(O, synth, 1280, 720)
+            line["cpu_baseline"]["c5_detect_describe"] = detect_cpu_baseline(O, synth, 3840, 2160)
         except Exception as e:
-            line["cpu_baseline"]["c2_detect_describe_error"] = repr(e)
-        try:
-            line["extra"]["c2_pipeline"] = c2_extra(clb, torch, synth)
-        except Exception as e:   # the headline number must still print
-            line["extra"]["c2_pipeline_error"] = repr(e)
-        try:
-            line["extra"]["c2_model_residuals"] = residuals_extra(clb, torch, O)
-        except Exception as e:
-            line["extra"]["c2_model_residuals_error"] = repr(e)
-        for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
-                       ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
+            line["cpu_baseline"]["detect_describe_error"] = repr(e)
+        for key, fn in (("c2_pipeline", lambda: frame_extra(clb, torch, synth, 1280, 720)), ("c5_pipeline", lambda: frame_extra(clb, torch, synth, 3840, 2160)),
+                        ("c2_model_residuals", lambda: residuals_extra(clb, torch, O)),
+                        ("reference_kernels_b200", lambda: reference_kernels_extra(clb, torch, O, synth))):
             try:
-                line["extra"][key] = stream_extra(clb, torch, synth, *a)
-            except Exception as e:
+                line["extra"][key] = fn()
+            except Exception as e:   # the headline number must still print
                 line["extra"][key + "_error"] = repr(e)
     emit(json.dumps(line))
 

@@ -114,6 +114,13 @@ def microbench_pipes(device=0):
     return dict(zip(k, [float(v) for v in out]))
 
 
+def microbench_mma(device=0):
+    out = (C.c_double * 6)()
+    _check(lib().clb_microbench_mma(int(device), out))
+    k = ["cycles_per_mma", "mac_per_clk_sm", "sm_mhz", "tflops", "sm_count", "mmas_per_sm"]
+    return dict(zip(k, [float(v) for v in out]))
+
+
 def _sarg(stream):
     """cudaStream_t argument: None -> NULL (= the object's own stream); a torch stream handle of 0 (the legacy
     default stream) is passed as cudaStreamLegacy (0x1) so that it is not mistaken for NULL."""

@@ -172,6 +172,12 @@ int clb_microbench_pipes(int device, double* out8) {
     return microbench_pipes(out8);
 }
 
+int clb_microbench_mma(int device, double* out6) {
+    if (!out6) return CLB_EINVAL;
+    CLB_CUDA(cudaSetDevice(device));
+    return microbench_mma(out6);
+}
+
 int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector** out) {
     if (!opts || !out) return CLB_EINVAL;
     if (opts->scale_levels < 1 || opts->scale_levels > CLB_MAX_LEVELS || opts->width < 1 || opts->height < 1 ||

@@ -151,5 +151,6 @@ int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t 
 int latch_init();   // uploads the triplet table
 // microbench.cu
 int microbench_pipes(double* out8);
+int microbench_mma(double* out6);      // match_tc.cu: bare tcgen05.mma kind::mxf4 stream on every SM
 
 }  // namespace clb

@@ -24,6 +24,8 @@
 //                   keys go through the same 3-op best/second update as match.cu.
 //   The per-(chunk, query) key pairs land in the same `partial` array match.cu's merge kernel folds.
 #include "common.cuh"
+#include <vector>
+#include <algorithm>
 
 namespace clb {
 
@@ -1137,6 +1139,126 @@ __global__ void __launch_bounds__(TC4_THREADS, 1)
 match_tc4_jobs_kernel(const TcJob* __restrict__ jobs) {
     const TcJob j = jobs[blockIdx.x];
     tc4_cta<false>(j.Q, j.nQ, j.Tx, j.qblock, j.tile0, j.ntiles, j.chunk_rows, j.partial_chunk, 0);
+}
+
+// ---- measured tensor-pipe peak (clb_microbench_mma) -------------------------------------------------------------------
+// A bare stream of the sweep's own instruction -- tcgen05.mma kind::mxf4.block_scale M128 N128 K64, A from TMEM, B from
+// shared memory, unit scales, +-1 E2M1 operands -- on every SM: no TMA feed, no epilogue, no hand-off.  What it sustains is
+// the roofline denominator of match_tc4_kernel (MEASURED_PEAKS.json has no fp4 figure).
+__global__ void __launch_bounds__(128, 1)
+tc_mma_bench_kernel(int groups, long long* __restrict__ cycles_out, unsigned long long* __restrict__ ns_out) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    const uint32_t raw = tc_smem_u32(tc_smem_raw);
+    const uint32_t sB = (raw + 1023u) & ~1023u;                   // two K-blocks of 16 KB
+    const uint32_t sBar = sB + 2 * TC_KB_BYTES;
+    const uint32_t bar_done = sBar, tmem_slot = sBar + 8;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(tc_smem_raw + (tmem_slot - raw));
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        tc_mbar_init(bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tmem_slot) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // +-1 nibbles, pseudo-random like real descriptors (the data decides the power drawn, and with it the clock)
+    uint32_t* bw = reinterpret_cast<uint32_t*>(tc_smem_raw + (sB - raw));
+    for (int i = tid; i < 2 * TC_KB_BYTES / 4; i += 128) {
+        uint32_t h = (uint32_t)i * 2654435761u + blockIdx.x * 40503u; h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        bw[i] = 0x22222222u | (h & 0x88888888u);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+    const uint32_t tm_sf = tmem + 256u, tm_a = tmem + 320u;
+    {
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        uint32_t r[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) r[c] = 0x7F7F7F7Fu;
+        tc_st32(lane_base + 256u, r); tc_st32(lane_base + 288u, r);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+#pragma unroll
+            for (int c = 0; c < 32; ++c) { uint32_t h = (uint32_t)(tid * 131 + q * 32 + c) * 2654435761u; h ^= h >> 15; r[c] = 0x22222222u | (h & 0x88888888u); }
+            tc_st32(lane_base + 320u + (uint32_t)(q * 32), r);
+        }
+        tc_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 0) {
+        const uint64_t desc_hi = ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+        long long c0 = clock64();
+        unsigned long long t0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (int j = 0; j < groups; ++j) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {          // one "DB tile" of the sweep: 2 accumulators x 2 K-blocks x 4 instructions
+                if (tc_elect_one()) {
+                    const uint64_t b0 = desc_hi | (uint64_t)(((sB + (g & 1) * TC_KB_BYTES) & 0x3FFFFu) >> 4);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        tc_mma_mxf4_ts(tmem + (uint32_t)((g >> 1) * TC_TILE), tm_a + (uint32_t)((g >> 1) * 64 + (g & 1) * 32 + k * 8), b0 + (uint64_t)(k * 2),
+                                       (uint32_t)(((g & 1) | k) != 0), tm_sf, tm_sf + 32u);
+                }
+                __syncwarp();
+            }
+        }
+        if (tc_elect_one()) tc_commit(bar_done);
+        __syncwarp();
+        tc_mbar_wait(bar_done, 0);
+        const long long c1 = clock64();
+        unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (lane == 0) { cycles_out[blockIdx.x] = c1 - c0; ns_out[blockIdx.x] = t1 - t0; }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+// out[0] cycles per MMA (median SM)  out[1] MAC per clock per SM  out[2] SM MHz while it ran (cycles / globaltimer)
+// out[3] chip TFLOP/s by CUDA events over the whole launch  out[4] SM count  out[5] MMAs per SM
+int microbench_mma(double* out6) {
+    int dev = 0, sms = 148;
+    CLB_CUDA(cudaGetDevice(&dev));
+    CLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int smem = 2 * TC_KB_BYTES + 64 + 1024;
+    CLB_CUDA(cudaFuncSetAttribute(tc_mma_bench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    long long* d_cyc = nullptr; unsigned long long* d_ns = nullptr;
+    CLB_CUDA(cudaMalloc(&d_cyc, sms * sizeof(long long)));
+    CLB_CUDA(cudaMalloc(&d_ns, sms * sizeof(unsigned long long)));
+    cudaEvent_t e0, e1;
+    CLB_CUDA(cudaEventCreate(&e0)); CLB_CUDA(cudaEventCreate(&e1));
+    const int groups = 20000;                    // 320 000 MMAs per SM: ~10 ms, long enough for the clock to settle
+    float ms = 0.f;
+    for (int rep = 0; rep < 3; ++rep) {
+        cudaEventRecord(e0, 0);
+        tc_mma_bench_kernel<<<sms, 128, smem>>>(groups, d_cyc, d_ns);
+        cudaEventRecord(e1, 0);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) { cudaFree(d_cyc); cudaFree(d_ns); return set_cuda_error(e, "tc_mma_bench_kernel", __FILE__, __LINE__); }
+        cudaEventElapsedTime(&ms, e0, e1);
+    }
+    std::vector<long long> cyc(sms); std::vector<unsigned long long> ns(sms);
+    cudaMemcpy(cyc.data(), d_cyc, sms * sizeof(long long), cudaMemcpyDeviceToHost);
+    cudaMemcpy(ns.data(), d_ns, sms * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaFree(d_cyc); cudaFree(d_ns); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    std::vector<double> per(sms), mhz(sms);
+    const double mmas = 16.0 * groups;
+    for (int i = 0; i < sms; ++i) { per[i] = (double)cyc[i] / mmas; mhz[i] = ns[i] ? 1e3 * (double)cyc[i] / (double)ns[i] : 0.0; }
+    std::sort(per.begin(), per.end()); std::sort(mhz.begin(), mhz.end());
+    const double mac = (double)TC_TILE * TC_TILE * 64.0;
+    out6[0] = per[sms / 2]; out6[1] = mac / per[sms / 2]; out6[2] = mhz[sms / 2];
+    out6[3] = 2.0 * mac * mmas * sms / (ms * 1e-3) / 1e12; out6[4] = sms; out6[5] = mmas;
+    return CLB_OK;
 }
 
 // ---- host side --------------------------------------------------------------------------------

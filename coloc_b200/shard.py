@@ -9,8 +9,9 @@
     contiguous slices; no exchange inside the data path, only a gather of the int32 match lists
     (-1 = none: the reference's g_match format, CUDAK2NN.cu:75).
 
-torch / torch.distributed are plumbing here (device buffers, NCCL or gloo collectives); all
-arithmetic is in libcoloc_b200.so.  The pure index helpers at the top are CPU-testable (gloo).
+The sharded matcher itself lives in the C ABI (clb_sharded_*, coloc_b200/csrc/api_sharded.cu; Python binding
+coloc_b200.ShardedMatcher): sweep + ncclAllGather + merge inside the library.  This module keeps the pure index helpers
+(shard ranges, the pair / row plan) that bench.py and the CPU (gloo) tests share.
 """
 import numpy as np
 
@@ -41,58 +42,6 @@ def pair_row_plan(pairs, counts, rank, world):
             out.append((p, a - off, b - off))
         off += n
     return out
-
-
-class ShardedMatcher:
-    """DB-row-sharded 2-NN over a torch.distributed process group (NCCL on GPUs).
-
-    set_shard() uploads this rank's DB rows once (GPUMatcher::setMapData analogue); match() is the
-    per-frame call: H2D of the queries, local partial, all-gather, device merge, D2H of match[]."""
-
-    def __init__(self, matcher, group=None):
-        import torch
-        import torch.distributed as dist
-        self.torch, self.dist = torch, dist
-        self.m = matcher
-        self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.dT = None
-        self.n_local = 0
-        self.t_base = 0
-
-    def set_shard_dev(self, dT_rows, t_base):
-        """dT_rows: int64 CUDA tensor [n_local, 8] (device-resident shard), t_base: global index of row 0."""
-        self.dT, self.n_local, self.t_base = dT_rows, int(dT_rows.shape[0]), int(t_base)
-        # resident shard: copied and expanded once inside the matcher (GPUMatcher::setMapData analogue), not per step
-        self.m.set_map_dev(dT_rows, self.n_local, stream=self.torch.cuda.current_stream().cuda_stream)
-
-    def set_shard(self, T_rows_host, t_base):
-        t = self.torch.from_numpy(np.ascontiguousarray(T_rows_host, np.uint64).view(np.int64).reshape(-1, 8))
-        self.set_shard_dev(t.cuda(non_blocking=False), t_base)
-
-    def match_dev(self, dQ, nQ, threshold, d_out, parts_buf=None, gather_buf=None):
-        """device-resident step.  d_out: int32 CUDA tensor [3, nQ] (match, best, second).  Enqueues on torch's
-        current stream; returns nothing."""
-        torch, dist = self.torch, self.dist
-        stream = torch.cuda.current_stream().cuda_stream   # 0 (legacy default) is mapped to cudaStreamLegacy by the binding
-        if self.world == 1:
-            self.m.match_map_dev(dQ, nQ, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
-            return
-        local = parts_buf if parts_buf is not None else torch.empty((nQ, 4), dtype=torch.int32, device=dQ.device)
-        allp = gather_buf if gather_buf is not None else torch.empty((self.world, nQ, 4), dtype=torch.int32, device=dQ.device)
-        self.m.match_map_partial_dev(dQ, nQ, self.t_base, local, stream=stream)
-        dist.all_gather_into_tensor(allp.view(-1), local.view(-1), group=self.group)   # the one exchange step
-        self.m.merge_partials_dev(allp, self.world, nQ, threshold, d_out[0], d_out[1], d_out[2], stream=stream)
-
-    def match(self, Q_host_pinned, threshold):
-        """end-to-end step from HOST queries (pinned torch int64 [nQ, 8]) to a HOST match list."""
-        torch = self.torch
-        nQ = int(Q_host_pinned.shape[0])
-        dQ = Q_host_pinned.cuda(non_blocking=True)
-        out = torch.empty((3, nQ), dtype=torch.int32, device=dQ.device)
-        self.match_dev(dQ, nQ, threshold, out)
-        return out[0].cpu()
 
 
 def gather_partials(local_parts, group=None):

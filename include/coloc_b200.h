@@ -323,6 +323,10 @@ int  clb_model_residuals_dev(clb_matcher* m, int kind, const double* d_models, i
  * out[4]=SM MHz during the run  out[5]=SM count
  * out[6]=chip G POPC32/s (wall time)  out[7]=chip G LOP3/s (wall time) */
 int  clb_microbench_pipes(int device, double* out8);
+/* measured tensor-pipe peak behind match_tc4_kernel's roofline: a bare stream of the sweep's own instruction (tcgen05.mma
+ * kind::mxf4.block_scale M128 N128 K64, A in TMEM, B in shared memory, +-1 operands) on every SM, ~10 ms.
+ * out[0]=cycles per MMA  out[1]=MAC/clk/SM  out[2]=SM MHz while it ran  out[3]=chip TFLOP/s (CUDA events)  out[4]=SMs  out[5]=MMAs per SM */
+int  clb_microbench_mma(int device, double* out6);
 /* number of kernels this library launched on the calling process so far (bench's gpu_launches) */
 int64_t clb_launch_count(void);
 /* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */
