@@ -44,9 +44,16 @@ struct clb_detector {
     size_t level_off[CLB_MAX_LEVELS];
     LevelTex tex;        // texture views of the pyramid levels for the frame geometry tex_w x tex_h
     int tex_w, tex_h, tex_n;
+    bool tex_fresh;      // texture objects created since the last describe launch: that launch must be a plain one (see run_pipeline)
     cudaStream_t copy_stream;   // keypoint D2H of the blocking per-frame call, behind the describe kernel
-    cudaEvent_t ev_count;
+    cudaEvent_t ev_count, ev_fast;
     bool copy_ready;
+    // per frame geometry (rebuilt when w x h changes): TMA tensor maps of the levels, the resize kernel's source-box plan and
+    // its column / row tables
+    LevelMaps maps;
+    ResizePlan rplan;
+    DevBuf rtab;
+    int geo_w, geo_h;
     int fast_quirk;      // 1 = the compiled reference's KFAST column walk (KFAST.h:243 `1 << 32`), 0 = every column scanned
 };
 
@@ -79,6 +86,49 @@ static size_t make_table(clb_detector* d, int w, int h, LevelTable& lt) {
     return off;
 }
 
+// tensor maps of the FAST tiles, one per level (the only maps a single-level call needs)
+static int make_fast_maps(const LevelTable& lt, LevelMaps& maps) {
+    int bw = 0, bh = 0;
+    fast_tile_box(&bw, &bh);
+    for (int L = 0; L < lt.n; ++L) {
+        if (!lt.img[L] || lt.w[L] < 1 || lt.h[L] < 1) continue;
+        const int rc = make_tmap_2d(&maps.fast[L], lt.img[L], 1, (uint64_t)lt.w[L], (uint64_t)lt.h[L], (uint64_t)lt.stride[L], (uint32_t)bw, (uint32_t)bh);
+        if (rc) return rc;
+    }
+    return CLB_OK;
+}
+
+// everything that depends on the frame geometry only: tensor maps, resize plan + tables (the pyramid buffer itself never moves)
+static int ensure_geometry(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
+    if (d->geo_w == lt.w[0] && d->geo_h == lt.h[0]) return CLB_OK;
+    d->geo_w = d->geo_h = 0;
+    memset(&d->maps, 0, sizeof(d->maps));
+    int rc = make_fast_maps(lt, d->maps);
+    if (rc) return rc;
+    rc = resize_plan(lt, d->rplan);
+    if (rc) return rc;
+    for (int L = 1; L < lt.n; ++L) {
+        if (lt.w[L] < 1 || lt.h[L] < 1) continue;
+        rc = make_tmap_2d(&d->maps.resize[L], lt.img[0], 1, (uint64_t)lt.w[0], (uint64_t)lt.h[0], (uint64_t)lt.stride[0],
+                          (uint32_t)d->rplan.box_w[L], (uint32_t)d->rplan.box_h[L]);
+        if (rc) return rc;
+    }
+    // the previous geometry's tables may still be read by work queued on another stream of this detector
+    CLB_CUDA(cudaDeviceSynchronize());
+    CLB_CUDA(d->rtab.reserve(resize_table_entries(lt) * sizeof(uint2)));
+    d->rplan.tab = d->rtab.as<uint2>();
+    rc = launch_resize_tables(lt, d->rplan, d->rtab.as<uint2>(), s);
+    if (rc) return rc;
+    d->geo_w = lt.w[0]; d->geo_h = lt.h[0];
+    return CLB_OK;
+}
+
+static int resize_frame(clb_detector* d, const LevelTable& lt, cudaStream_t s, bool pdl) {
+    uint32_t* clear = nullptr; int words = 0;
+    fast_clear_region(lt, d->fast_scratch.p, &clear, &words);
+    return launch_resize(lt, d->rplan, d->maps, clear, words, s, pdl);
+}
+
 // texture views follow the frame geometry (the pyramid buffer itself never moves)
 static int ensure_textures(clb_detector* d, const LevelTable& lt, int w, int h) {
     if (d->tex_n == lt.n && d->tex_w == w && d->tex_h == h) return CLB_OK;
@@ -86,9 +136,16 @@ static int ensure_textures(clb_detector* d, const LevelTable& lt, int w, int h) 
     d->tex_n = 0;
     int rc = make_level_textures(lt, d->tex);
     if (rc) return rc;
-    d->tex_n = lt.n; d->tex_w = w; d->tex_h = h;
+    d->tex_n = lt.n; d->tex_w = w; d->tex_h = h; d->tex_fresh = true;
     return CLB_OK;
 }
+
+// The describe kernel joins the frame's programmatic-dependent-launch chain EXCEPT on the first launch after its texture objects
+// were (re)created: a programmatically launched grid can start on SMs whose texture-header cache still holds the header a
+// destroyed object left in the same slot (measured: the first frame of a detector created after another one was destroyed had
+// 1/7 of its descriptors -- one GPC's CTAs -- computed from the old header); a plain launch goes through the full kernel
+// boundary that applies the invalidation.
+static bool describe_pdl(clb_detector* d) { const bool pdl = !d->tex_fresh; d->tex_fresh = false; return pdl; }
 
 extern "C" {
 
@@ -187,8 +244,8 @@ int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector*
     CLB_CUDA(cudaSetDevice(device));
     clb_detector* d = new (std::nothrow) clb_detector();
     if (!d) return CLB_ENOMEM;
-    d->o = *opts; d->device = device; d->h_total = nullptr; d->fast_quirk = 1;
-    memset(&d->tex, 0, sizeof(d->tex)); d->tex_w = d->tex_h = d->tex_n = 0;
+    d->o = *opts; d->device = device; d->h_total = nullptr; d->fast_quirk = 1; d->geo_w = d->geo_h = 0;
+    memset(&d->tex, 0, sizeof(d->tex)); d->tex_w = d->tex_h = d->tex_n = 0; d->tex_fresh = false;
     cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMallocHost(&d->h_total, 64);
@@ -211,9 +268,9 @@ void clb_detector_destroy(clb_detector* d) {
     if (!d) return;
     cudaSetDevice(d->device);
     destroy_level_textures(d->tex, d->tex_n);
-    d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release();
+    d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release(); d->rtab.release();
     if (d->h_total) cudaFreeHost(d->h_total);
-    if (d->copy_ready) { cudaEventDestroy(d->ev_count); cudaStreamDestroy(d->copy_stream); }
+    if (d->copy_ready) { cudaEventDestroy(d->ev_count); cudaEventDestroy(d->ev_fast); cudaStreamDestroy(d->copy_stream); }
     if (d->stream) cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -244,15 +301,17 @@ static int check_frame(clb_detector* d, int w, int h, int stride) {
 }
 
 // device pipeline on a level-0 image already inside d->pyr (table lt)
+// resize -> [scan ends] -> FAST score + NMS -> compaction + orientation -> LATCH, chained by programmatic dependent launch:
+// each kernel's CTAs are scheduled while the one in front drains and wait (griddepcontrol.wait) before they read its output
 static int run_pipeline(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
     int rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
     if (rc) return rc;
-    rc = launch_resize(lt, s);
+    rc = resize_frame(d, lt, s, true);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    rc = launch_fast(lt, d->maps, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, true, false);
     if (rc) return rc;
-    return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex);
+    return launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex, describe_pdl(d));
 }
 
 int clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h, int stride,
@@ -264,6 +323,8 @@ int clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h
     cudaStream_t s = stream ? (cudaStream_t)stream : d->stream;
     LevelTable lt;
     make_table(d, w, h, lt);
+    rc = ensure_geometry(d, lt, s);
+    if (rc) return rc;
     CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], d_gray, stride, w, h, cudaMemcpyDeviceToDevice, s));
     rc = run_pipeline(d, lt, s);
     if (rc) return rc;
@@ -285,25 +346,31 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
     cudaStream_t s = d->stream;
     LevelTable lt;
     make_table(d, w, h, lt);
+    rc = ensure_geometry(d, lt, s);
+    if (rc) return rc;
     CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], gray, stride, w, h, cudaMemcpyHostToDevice, s));
     if (!d->copy_ready) {
         CLB_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
         CLB_CUDA(cudaEventCreateWithFlags(&d->ev_count, cudaEventDisableTiming));
+        CLB_CUDA(cudaEventCreateWithFlags(&d->ev_fast, cudaEventDisableTiming));
         d->copy_ready = true;
     }
-    // the keypoints are final after the FAST stage: their count comes back while the describe kernel runs, and the keypoint
-    // D2H copy goes out on a second stream behind that kernel; only the descriptor copy follows it
+    // the keypoints are final after the FAST stage: their count comes back on a second stream while the describe kernel runs
+    // (so the kernels of the frame stay one programmatic-dependent-launch chain), and the keypoint D2H copy follows it there;
+    // only the descriptor copy comes behind the describe kernel
     rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
     if (rc) return rc;
-    rc = launch_resize(lt, s);
+    rc = resize_frame(d, lt, s, true);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    rc = launch_fast(lt, d->maps, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, true, false);
     if (rc) return rc;
-    CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CLB_CUDA(cudaEventRecord(d->ev_count, s));
-    rc = launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex);
+    CLB_CUDA(cudaEventRecord(d->ev_fast, s));
+    rc = launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex, describe_pdl(d));
     if (rc) return rc;
+    CLB_CUDA(cudaStreamWaitEvent(d->copy_stream, d->ev_fast, 0));
+    CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, d->copy_stream));
+    CLB_CUDA(cudaEventRecord(d->ev_count, d->copy_stream));
     CLB_CUDA(cudaEventSynchronize(d->ev_count));
     const int n = *d->h_total;
     *n_out = n;
@@ -329,8 +396,10 @@ int clb_pyramid(clb_detector* d, const uint8_t* gray, int w, int h, int stride, 
     cudaStream_t s = d->stream;
     LevelTable lt;
     make_table(d, w, h, lt);
+    rc = ensure_geometry(d, lt, s);
+    if (rc) return rc;
     CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], gray, stride, w, h, cudaMemcpyHostToDevice, s));
-    rc = launch_resize(lt, s);
+    rc = resize_frame(d, lt, s, false);
     if (rc) return rc;
     size_t off = 0;
     for (int i = 0; i < lt.n; ++i) {
@@ -355,7 +424,10 @@ int clb_fast_nms_angle(clb_detector* d, const uint8_t* level, int w, int h, int 
     lt.img[0] = d->pyr.as<uint8_t>();
     CLB_CUDA(cudaMemcpy2DAsync(d->pyr.p, lt.stride[0], level, stride, w, h, cudaMemcpyHostToDevice, s));
     int* d_total = d->misc.as<int>();
-    rc = launch_fast(lt, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s);
+    LevelMaps one; memset(&one, 0, sizeof(one));
+    rc = make_fast_maps(lt, one);
+    if (rc) return rc;
+    rc = launch_fast(lt, one, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, false, true);
     if (rc) return rc;
     CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, s));
     CLB_CUDA(cudaStreamSynchronize(s));
@@ -510,6 +582,8 @@ int clb_stream_submit(clb_stream* s, const uint8_t* gray, int w, int h, int stri
         for (int y = 0; y < h; ++y) memcpy(sl.h_img + (size_t)y * w, gray + (size_t)y * stride, (size_t)w);
         src = sl.h_img; src_stride = w;
     }
+    rc = ensure_geometry(d, lt, st);
+    if (rc) return rc;
     CLB_CUDA(cudaMemcpy2DAsync(const_cast<uint8_t*>(lt.img[0]), lt.stride[0], src, src_stride, w, h, cudaMemcpyHostToDevice, st));
     rc = run_pipeline(d, lt, st);
     if (rc) return rc;

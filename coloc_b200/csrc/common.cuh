@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host helpers for libcoloc_b200 (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda.h>        // CUtensorMap (types only; the driver entry point is looked up at run time, tmap.cu)
 #include <stdint.h>
 #include <stdio.h>
 #include <atomic>
@@ -76,6 +77,51 @@ struct DevBuf {
 
 }  // namespace clb
 
+// ---- TMA / mbarrier PTX shared by the image kernels ----------------------------------------------
+namespace clb {
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t ptx_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void ptx_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ptx_smem(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void ptx_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(ptx_smem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ptx_mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(ptx_smem(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+// one box of a 2-D tensor map -> shared memory (SASS UTMALDG); rows / columns outside the tensor are zero-filled
+__device__ __forceinline__ void ptx_tma_load_2d(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(ptx_smem(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(ptx_smem(bar)) : "memory");
+}
+// programmatic dependent launch: wait for the grids this one depends on / let the dependent grid start its prologue
+__device__ __forceinline__ void ptx_grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void ptx_grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+#ifdef __CUDACC__
+// kernel launch with the programmatic-dependent-launch attribute (the kernel calls griddepcontrol.wait before it touches what
+// the grid in front of it wrote): its CTAs are scheduled while that grid drains instead of after it
+template <class... KArgs, class... Args>
+inline cudaError_t launch_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem, uint64_t w_elems, uint64_t h, uint64_t stride, uint32_t box_w, uint32_t box_h);
+}  // namespace clb
+
 // ---- stage launchers (defined in the .cu files) --------------------------------------------------
 namespace clb {
 
@@ -137,16 +183,33 @@ int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s);
 int tc_plan_pairs(const int* nQ, const int* nT, int npairs, int sm_count, double* t_us_out = nullptr);   // -> DB tiles per chunk, shared by all pairs (+ modelled time)
 int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s);
 int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int threshold, float ratio, cudaStream_t s);
+// TMA tensor maps of one frame geometry (tmap.cu builds them, the detector caches them per (w, h)):
+//   fast[L]    8-bit map over level L, box = the FAST tile + halo (80 x 40)
+//   resize[L]  8-bit map over LEVEL 0, box = the source footprint of one output tile of level L
+struct alignas(64) LevelMaps {
+    CUtensorMap fast[CLB_MAX_LEVELS];
+    CUtensorMap resize[CLB_MAX_LEVELS];
+};
 // pyramid.cu
-int launch_resize(const LevelTable& lt, cudaStream_t s);   // fills levels 1..n-1 from level 0
+struct ResizePlan {            // per-level source-box geometry + the column / row tables of every level, device-resident
+    int tile_w[CLB_MAX_LEVELS], tile_h[CLB_MAX_LEVELS];   // output tile of a CTA (64 x 16 unless the scale is extreme)
+    int box_w[CLB_MAX_LEVELS], box_h[CLB_MAX_LEVELS];     // bytes x rows staged per output tile (box_w a multiple of 16, <= 256)
+    int col_off[CLB_MAX_LEVELS], row_off[CLB_MAX_LEVELS]; // first table entry of each level
+    const uint2* tab;                                      // entries {origin (bit 31 = clamped at the edge), weight}
+};
+size_t resize_table_entries(const LevelTable& lt);
+int resize_plan(const LevelTable& lt, ResizePlan& rp);                                  // box geometry (host)
+int launch_resize_tables(const LevelTable& lt, const ResizePlan& rp, uint2* d_tab, cudaStream_t s);
+int launch_resize(const LevelTable& lt, const ResizePlan& rp, const LevelMaps& maps, uint32_t* clear, int clear_words, cudaStream_t s, bool pdl = false);   // fills levels 1..n-1 from level 0; also zeroes clear[0..clear_words)
 // fast.cu
-struct FastScratch { uint8_t* nms; int* row_count; int* row_off; int* total; };
 size_t fast_scratch_bytes(const LevelTable& lt);
-int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size_t scratch_bytes,
-                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s);
+int fast_tile_box(int* w, int* h);
+int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int quirk, void* scratch, size_t scratch_bytes,
+                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s, bool pdl = false, bool standalone = true);
+void fast_clear_region(const LevelTable& lt, void* scratch, uint32_t** ptr, int* words);
 // latch.cu
 int launch_describe(const LevelTable& lt, const clb_keypoint* d_kps, int n, const int* d_n, int cap,
-                    uint64_t* d_desc, cudaStream_t s, const LevelTex* tex = nullptr);
+                    uint64_t* d_desc, cudaStream_t s, const LevelTex* tex = nullptr, bool pdl = false);
 int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t s);
 int latch_init();   // uploads the triplet table
 // microbench.cu

@@ -67,6 +67,8 @@ __device__ __forceinline__ bool fast_pretest(const uint8_t* __restrict__ p, int 
 __global__ void __launch_bounds__(256)
 fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int thresh, int* __restrict__ xend) {
     __shared__ uint32_t sbits[8][FQ_WORDS];
+    ptx_grid_dep_wait();                // every CTA: the level comes from the resize kernel, and the score kernel behind this
+    ptx_grid_dep_launch();              // one relies on this grid not finishing before that one has
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qrow = blockIdx.x * 8 + wid;
     if (qrow >= qr.row_base[qr.n]) return;
@@ -363,10 +365,11 @@ angle_kernel(const LevelTable lt, clb_keypoint* __restrict__ kps, const int* __r
 //   score    queue 2: sliding min/max of width 9, score byte into the shared score map
 //   nms      queue 2 again: 8 neighbours of each corner of the output tile, survivors into the output map + row counts
 //   output   one 32-bit word (4 px) per thread to the global map
-template <int TH>
+template <int TH, bool TMA = false>
 struct Fast2 {
     static constexpr int SH = TH + 8;              // staged rows: gy = y0 - 4 + r
-    static constexpr int SSTR = 80;                // staged cols: gx = x0 - 8 + j
+    static constexpr int XO = TMA ? 16 : 8;        // staged cols: gx = x0 - XO + j (a TMA box starts on a 16-byte boundary)
+    static constexpr int SSTR = TMA ? 96 : 80;
     static constexpr int CW = FT_TW + 2, CH = TH + 2;   // score region: gx = x0 - 1 + c, gy = y0 - 1 + r
     static constexpr int CSTR = 72;                // score byte (r, c) at r * CSTR + c + 3: output col 0 is word aligned
     static constexpr int NPOS = CH * CW;
@@ -379,12 +382,17 @@ __device__ __forceinline__ void fast_ring(const uint8_t* __restrict__ p, int str
     ring[12] = p[-3];             ring[13] = p[stride - 3];     ring[14] = p[2 * stride - 2];  ring[15] = p[3 * stride - 1];
 }
 
-template <int TH, int MINB, bool SWAR>
+// TMA = the tile + halo arrives by ONE cp.async.bulk.tensor.2d (SASS UTMALDG) from the level's tensor map: box 96 x (TH + 8)
+// at (x0 - 16, y0 - 4) (a box starts on a 16-byte boundary), rows / columns outside the level zero-filled by the copy engine (border pixels are never scored, so
+// zero is as good as the clamped values the load loop staged); the staging loop and its per-lane address arithmetic -- a
+// fifth of the kernel's instructions in the ncu source view -- are gone.
+template <int TH, int MINB, bool SWAR, bool TMA>
 __global__ void __launch_bounds__(256, MINB)
-fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __restrict__ nms_map,
+fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ LevelMaps maps, int thresh, uint8_t* __restrict__ nms_map,
                  int do_nms, int* __restrict__ row_count, uint32_t* __restrict__ bitmap, const int* __restrict__ xend) {
-    typedef Fast2<TH> F;
-    __shared__ __align__(16) uint8_t px[F::SH * F::SSTR];
+    typedef Fast2<TH, TMA> F;
+    __shared__ __align__(128) uint8_t px[F::SH * F::SSTR];
+    __shared__ __align__(8) uint64_t bar;
     __shared__ __align__(16) uint8_t sc[F::CH * F::CSTR];
     __shared__ __align__(16) uint8_t so[TH * FT_TW];
     __shared__ uint16_t q1[F::NPOS], q2[F::NPOS];
@@ -399,8 +407,17 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
     const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * TH;
     const int tid = threadIdx.x, lane = tid & 31;
 
+    if (TMA && tid == 0) {
+        ptx_mbar_init(&bar, 1);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        ptx_grid_dep_wait();            // the level is written by the resize kernel in front of this one
+        ptx_mbar_expect_tx(&bar, (uint32_t)(F::SH * F::SSTR));
+        ptx_tma_load_2d(px, &maps.fast[L], x0 - F::XO, y0 - 4, &bar);
+    }
+    ptx_grid_dep_launch();
     if (tid == 0) { n1 = 0; n2 = 0; }
     if (tid < TH) rowcnt[tid] = 0;
+    if (!TMA || ((rm.quirk_mask >> L) & 1u)) ptx_grid_dep_wait();      // xend[] comes from the kernel in front as well
     if (tid < F::CH) {                 // scan end of each score-region row: w - 3, or the reference's column walk (fast_xend_kernel)
         const int gy = y0 - 1 + tid;
         s_xlim[tid] = (((rm.quirk_mask >> L) & 1u) && gy >= 3 && gy < h - 3) ? __ldg(xend + rm.row_base[L] + gy) : w - 3;
@@ -410,7 +427,9 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
 
     // stage
     const bool wide = x0 >= 8 && x0 + F::SSTR - 8 <= w && (stride & 7) == 0 && (reinterpret_cast<uintptr_t>(img) & 7) == 0;
-    if (wide) {
+    if (TMA) {
+        // nothing to do: the box is in flight
+    } else if (wide) {
         for (int i = tid; i < F::SH * 10; i += 256) {          // x0 - 8 is 8-byte aligned
             const int r = i / 10, q = i - r * 10;
             const int gy = min(max(y0 - 4 + r, 0), h - 1);
@@ -435,6 +454,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
         }
     }
     __syncthreads();
+    if (TMA) ptx_mbar_wait(&bar, 0);
 
     // pre-test -> q1
     if (SWAR) {
@@ -459,7 +479,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
                 const int nlow = min(max(xlo - gxb, 0), 4), nval = min(max(xhi - gxb, 0), 4);
                 const uint32_t vmask = (0xFu << nlow) & ((1u << nval) - 1u);
                 if (gy >= 3 && gy < h - 3 && vmask) {
-                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(&px[(r + 3) * F::SSTR + 4 + 4 * wq]);
+                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(&px[(r + 3) * F::SSTR + (F::XO - 4) + 4 * wq]);
                     const uint32_t cw = wp[0], cl = wp[-1], cr = wp[1];
                     const uint32_t nw = wp[-3 * F::SSTR / 4], sw = wp[3 * F::SSTR / 4];
                     const uint32_t ew = __byte_perm(cw, cr, 0x6543), ww = __byte_perm(cl, cw, 0x4321);
@@ -503,7 +523,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
             const int r = i / F::CW, c = i - r * F::CW;
             const int gx = x0 - 1 + c, gy = y0 - 1 + r;
             if (gx >= 3 && gx < s_xlim[r] && gy >= 3 && gy < h - 3) {
-                const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+                const uint8_t* p = &px[(r + 3) * F::SSTR + (c + F::XO - 1)];
                 const int cv = p[0];
                 const int pn = p[-3 * F::SSTR], ps = p[3 * F::SSTR], pe = p[3], pw = p[-3];
                 const int bright = min(max(pn, ps), max(pe, pw));
@@ -530,7 +550,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
         if (k < c1) {
             i = q1[k];
             const int r = i / F::CW, c = i - r * F::CW;
-            const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+            const uint8_t* p = &px[(r + 3) * F::SSTR + (c + F::XO - 1)];
             const int cv = p[0];
             const int hi = cv + thresh, lo = cv - thresh;
             int ring[16];
@@ -563,7 +583,7 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __re
     for (int k = tid; k < c2; k += 256) {
         const int i = q2[k];
         const int r = i / F::CW, c = i - r * F::CW;
-        const uint8_t* p = &px[(r + 3) * F::SSTR + (c + 7)];
+        const uint8_t* p = &px[(r + 3) * F::SSTR + (c + F::XO - 1)];
         const int cv = p[0];
         int ring[16];
         fast_ring(p, F::SSTR, ring);
@@ -635,6 +655,8 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int nrows = rm.row_base[rm.n];
     const int grow0 = blockIdx.x * 8, grow = grow0 + wid;
+    ptx_grid_dep_wait();                // the score map, row counts and tile bitmap of the kernel in front
+    ptx_grid_dep_launch();
     int acc = 0;
     for (int i = tid; i < grow0; i += 256) acc += __ldg(row_count + i);
 #pragma unroll
@@ -754,15 +776,18 @@ size_t fast_scratch_bytes(const LevelTable& lt) {
     return map + 3 * ((rows * sizeof(int) + 255) & ~(size_t)255) + ((rows * bm_words * 4 + 255) & ~(size_t)255) + 256;
 }
 
-int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size_t scratch_bytes,
-                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s) {
+int fast_tile_box(int* w, int* h) { *w = Fast2<32, true>::SSTR; *h = Fast2<32, true>::SH; return CLB_OK; }
+
+// standalone = no resize kernel ran in front (stage-level entry point): the row counters are cleared here
+int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int quirk, void* scratch, size_t scratch_bytes,
+                clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s, bool pdl, bool standalone) {
     if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
     RowMap rm = make_rowmap(lt);
     const size_t rows = rm.row_base[lt.n];
     const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
     const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
     uint8_t* nms = reinterpret_cast<uint8_t*>(scratch);
-    // [map][row_count][tile bitmap][row_off][xend]: the counts and the bitmap are cleared by one memset
+    // [map][row_count][tile bitmap][row_off][xend]: the counts and the bitmap are cleared together (by the resize kernel)
     rm.bm_words = (int)((((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32);
     const size_t bm_bytes = (rows * (size_t)rm.bm_words * 4 + 255) & ~(size_t)255;
     int* row_count = reinterpret_cast<int*>(nms + map_bytes);
@@ -771,7 +796,7 @@ int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size
     const int fvar = g_fast_var, fnms = g_fast_nms;
     (void)fnms;
     const bool use_bm = (fvar & 35) == 35;       // bit 5: the tail visits occupied tiles only (needs both v2 kernels)
-    CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes + (use_bm ? bm_bytes : 0), s));
+    if (standalone) CLB_CUDA(cudaMemsetAsync(row_count, 0, cnt_bytes + bm_bytes, s));
     timer("fast").begin(s);
     // the reference's per-row scan end on the widths its `1 << 32` bites (quirk = 1): one small launch over those levels' rows
     QuirkRows qr; qr.n = 0; qr.row_base[0] = 0;
@@ -783,24 +808,25 @@ int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size
             qr.level[qr.n] = L; qr.row_base[qr.n + 1] = qr.row_base[qr.n] + lt.h[L]; ++qr.n;
         }
         if (qr.n > 0) {
-            fast_xend_kernel<<<(qr.row_base[qr.n] + 7) / 8, 256, 0, s>>>(lt, rm, qr, thresh, xend);
+            CLB_CUDA(launch_ex(fast_xend_kernel, dim3((qr.row_base[qr.n] + 7) / 8), dim3(256), 0, s, pdl, lt, rm, qr, thresh, xend));
             CLB_LAUNCHED();
         }
     }
 #ifdef CLB_LAB
     int* row_off = reinterpret_cast<int*>(nms + map_bytes + cnt_bytes + bm_bytes);
     if (fvar & 1) {
-        typedef void (*k2_t)(const LevelTable, const RowMap, int, uint8_t*, int, int*, uint32_t*, const int*);
+        typedef void (*k2_t)(const LevelTable, const RowMap, const LevelMaps, int, uint8_t*, int, int*, uint32_t*, const int*);
         static const k2_t k2[2][2][2] = {      // [64x32 tiles][8 CTAs per SM][16-bit-lane pre-test]
-            {{fast_nms2_kernel<16, 6, false>, fast_nms2_kernel<16, 6, true>}, {fast_nms2_kernel<16, 8, false>, fast_nms2_kernel<16, 8, true>}},
-            {{fast_nms2_kernel<32, 6, false>, fast_nms2_kernel<32, 6, true>}, {fast_nms2_kernel<32, 8, false>, fast_nms2_kernel<32, 8, true>}}};
+            {{fast_nms2_kernel<16, 6, false, false>, fast_nms2_kernel<16, 6, true, false>}, {fast_nms2_kernel<16, 8, false, false>, fast_nms2_kernel<16, 8, true, false>}},
+            {{fast_nms2_kernel<32, 6, false, false>, fast_nms2_kernel<32, 6, true, false>}, {fast_nms2_kernel<32, 8, false, false>, fast_nms2_kernel<32, 8, true, false>}}};
         const int big = (fvar & 4) ? 1 : 0, th = big ? 32 : 16;
         for (int L = 0; L < lt.n; ++L) {
             rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
             rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + th - 1) / th);
         }
         const int ntiles = rm.tile_base[lt.n];
-        k2[big][(fvar & 8) ? 1 : 0][(fvar & 16) ? 1 : 0]<<<ntiles, 256, 0, s>>>(lt, rm, thresh, nms, fnms, row_count, use_bm ? bitmap : nullptr, xend);
+        k2_t kern = fvar == 55 ? (k2_t)fast_nms2_kernel<32, 6, true, true> : k2[big][(fvar & 8) ? 1 : 0][(fvar & 16) ? 1 : 0];   // 55 = the product kernel (TMA-staged)
+        CLB_CUDA(launch_ex(kern, dim3(ntiles), dim3(256), 0, s, pdl, lt, rm, maps, thresh, nms, fnms, row_count, use_bm ? bitmap : (uint32_t*)nullptr, (const int*)xend));
     } else {
         int tiles = 0;
         for (int L = 0; L < lt.n; ++L) tiles += ((lt.w[L] + FT_TW - 1) / FT_TW) * ((lt.h[L] + FT_TH - 1) / FT_TH);
@@ -808,7 +834,8 @@ int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size
     }
     CLB_LAUNCHED();
     if (fvar & 2) {
-        compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total, use_bm ? bitmap : nullptr);
+        CLB_CUDA(launch_ex(compact2_kernel, dim3(((int)rows + 7) / 8), dim3(256), 0, s, pdl, lt, rm, (const uint8_t*)nms, (const int*)row_count, d_kps, cap, d_total,
+                           use_bm ? (const uint32_t*)bitmap : (const uint32_t*)nullptr));
         CLB_LAUNCHED();
     } else {
         row_scan_kernel<<<1, 1024, 0, s>>>(row_count, (int)rows, row_off, d_total);
@@ -823,13 +850,25 @@ int launch_fast(const LevelTable& lt, int thresh, int quirk, void* scratch, size
         rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
         rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + 31) / 32);
     }
-    fast_nms2_kernel<32, 6, true><<<rm.tile_base[lt.n], 256, 0, s>>>(lt, rm, thresh, nms, 1, row_count, bitmap, xend);
+    CLB_CUDA(launch_ex(fast_nms2_kernel<32, 6, true, true>, dim3(rm.tile_base[lt.n]), dim3(256), 0, s, pdl, lt, rm, maps, thresh, nms, 1, row_count, bitmap, (const int*)xend));
     CLB_LAUNCHED();
-    compact2_kernel<<<((int)rows + 7) / 8, 256, 0, s>>>(lt, rm, nms, row_count, d_kps, cap, d_total, bitmap);
+    CLB_CUDA(launch_ex(compact2_kernel, dim3(((int)rows + 7) / 8), dim3(256), 0, s, pdl, lt, rm, (const uint8_t*)nms, (const int*)row_count, d_kps, cap, d_total, (const uint32_t*)bitmap));
     CLB_LAUNCHED();
 #endif
     timer("fast").end(s);
     return CLB_OK;
+}
+
+// offset / length (32-bit words) of the row counters + tile bitmap inside the scratch buffer: the resize kernel clears them
+void fast_clear_region(const LevelTable& lt, void* scratch, uint32_t** ptr, int* words) {
+    size_t rows = 0;
+    for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
+    const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
+    const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
+    const size_t bm_words = ((size_t)((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32;
+    const size_t bm_bytes = (rows * bm_words * 4 + 255) & ~(size_t)255;
+    *ptr = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + map_bytes);
+    *words = (int)((cnt_bytes + bm_bytes) / 4);
 }
 
 }  // namespace clb
