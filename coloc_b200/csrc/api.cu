@@ -302,11 +302,15 @@ static int check_frame(clb_detector* d, int w, int h, int stride) {
 
 // device pipeline on a level-0 image already inside d->pyr (table lt)
 // resize -> [scan ends] -> FAST score + NMS -> compaction + orientation -> LATCH, chained by programmatic dependent launch:
-// each kernel's CTAs are scheduled while the one in front drains and wait (griddepcontrol.wait) before they read its output
+// each kernel's CTAs are scheduled while the one in front drains and wait (griddepcontrol.wait) before they read its output.
+// The resize kernel itself is a PLAIN launch: a programmatically launched grid does not get the L1 / texture-cache
+// invalidation of a kernel boundary (measured: with the whole chain programmatic, the describe kernel of frame 2 read
+// frame 1's keypoints out of L1 through its non-coherent loads), so every frame starts with one full boundary and the
+// kernels behind it only ever see lines that were fetched after their producer finished.
 static int run_pipeline(clb_detector* d, const LevelTable& lt, cudaStream_t s) {
     int rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
     if (rc) return rc;
-    rc = resize_frame(d, lt, s, true);
+    rc = resize_frame(d, lt, s, false);
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
     rc = launch_fast(lt, d->maps, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, true, false);
@@ -360,7 +364,7 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
     // only the descriptor copy comes behind the describe kernel
     rc = ensure_textures(d, lt, lt.w[0], lt.h[0]);
     if (rc) return rc;
-    rc = resize_frame(d, lt, s, true);
+    rc = resize_frame(d, lt, s, false);               // plain launch: the frame's one full kernel boundary (see run_pipeline)
     if (rc) return rc;
     int* d_total = d->misc.as<int>();
     rc = launch_fast(lt, d->maps, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, true, false);

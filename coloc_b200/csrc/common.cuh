@@ -192,7 +192,9 @@ struct alignas(64) LevelMaps {
 };
 // pyramid.cu
 struct ResizePlan {            // per-level source-box geometry + the column / row tables of every level, device-resident
-    int tile_w[CLB_MAX_LEVELS], tile_h[CLB_MAX_LEVELS];   // output tile of a CTA (64 x 16 unless the scale is extreme)
+    int tile_w[CLB_MAX_LEVELS], tile_h[CLB_MAX_LEVELS];   // output tile of a CTA (64 x 32 unless the scale is extreme)
+    int tile_base[CLB_MAX_LEVELS + 1], tiles_x[CLB_MAX_LEVELS];   // first tile of each level, tiles per tile row
+    uint32_t tiles_x_magic[CLB_MAX_LEVELS];                // tile / tiles_x == umulhi(tile, magic) (verified on the host)
     int box_w[CLB_MAX_LEVELS], box_h[CLB_MAX_LEVELS];     // bytes x rows staged per output tile (box_w a multiple of 16, <= 256)
     int col_off[CLB_MAX_LEVELS], row_off[CLB_MAX_LEVELS]; // first table entry of each level
     const uint2* tab;                                      // entries {origin (bit 31 = clamped at the edge), weight}

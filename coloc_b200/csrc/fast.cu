@@ -63,7 +63,25 @@ __device__ __forceinline__ bool fast_pretest(const uint8_t* __restrict__ p, int 
 // The walk starts at column 3 and looks at 32 columns: if some pass the pre-test but none of the first 16 does it advances by
 // 16, otherwise by 32.  With B = (w - 38) / 16 blocks of 16 columns in front of column w - 35, the walk either lands on block B
 // (32 columns left -> `(1 << 32) - 1` == 0 on x86 -> the tail is dropped, xend = w - 35) or steps over it (xend = w - 3).
-// One warp per row: ballots give the "any pre-test pass" bit of each 16-column block, lane 0 replays the walk.
+// One warp per row, four positions per lane and step (columns 3 + 128 i + 4 lane ..+3: one quarter of a 16-column block, read
+// as aligned 32-bit words of the three rows the pre-test touches, the loads of four steps in flight together -- the first
+// version walked 32 positions per step with byte loads and spent 22 us on a 1286 x 723 level waiting for them); two ballots
+// per step give the "any pre-test pass" bit of the step's eight blocks, lane 0 replays the walk.
+__device__ __forceinline__ uint32_t xend_pass4(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t n0, uint32_t n1, uint32_t s0, uint32_t s1, int t) {
+    // positions x .. x+3 with x = 4k + 3: centre / north / south bytes = (word0.b3, word1.b0..b2), west = word0.b0..b3,
+    // east = (word1.b2, word1.b3, word2.b0, word2.b1)
+    const uint32_t c = __byte_perm(w0, w1, 0x6543), n = __byte_perm(n0, n1, 0x6543), s = __byte_perm(s0, s1, 0x6543);
+    const uint32_t e = __byte_perm(w1, w2, 0x5432), wv = w0;
+    uint32_t any = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int cc = (c >> (8 * k)) & 255, nn = (n >> (8 * k)) & 255, ss = (s >> (8 * k)) & 255, ee = (e >> (8 * k)) & 255, ww = (wv >> (8 * k)) & 255;
+        const bool pass = (min(max(nn, ss), max(ee, ww)) > cc + t) | (max(min(nn, ss), min(ee, ww)) < cc - t);
+        any |= (uint32_t)pass << k;
+    }
+    return any;
+}
+
 __global__ void __launch_bounds__(256)
 fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int thresh, int* __restrict__ xend) {
     __shared__ uint32_t sbits[8][FQ_WORDS];
@@ -78,20 +96,43 @@ fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int t
     const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
     int* out = xend + rm.row_base[L] + y;
     if (y < 3 || y >= h - 3) { if (lane == 0) *out = w - 3; return; }
-    const uint8_t* __restrict__ row = lt.img[L] + (size_t)y * stride;
+    // rows are 128-byte aligned and at least w + 1 bytes of every row are addressable (stride = align_up(w, 128) > w - 12)
+    const uint32_t* __restrict__ rc = reinterpret_cast<const uint32_t*>(lt.img[L] + (size_t)y * stride);
+    const uint32_t* __restrict__ rn = reinterpret_cast<const uint32_t*>(lt.img[L] + (size_t)(y - 3) * stride);
+    const uint32_t* __restrict__ rs = reinterpret_cast<const uint32_t*>(lt.img[L] + (size_t)(y + 3) * stride);
     const int B = (w - 38) >> 4;                                  // blocks 0..B are looked at: columns 3 .. w - 20
-    uint32_t acc = 0;
-    int i = 0;
-    for (int x0 = 3; x0 <= w - 20; x0 += 32, ++i) {
-        const int x = x0 + lane;
-        const bool pass = x <= w - 20 && fast_pretest(row + x, stride, thresh);
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, pass);
-        acc |= (uint32_t)((bal & 0xFFFFu) != 0) << ((2 * i) & 31);
-        acc |= (uint32_t)((bal >> 16) != 0) << ((2 * i + 1) & 31);
-        if ((i & 15) == 15) { if (lane == 0) sbits[wid][i >> 4] = acc; acc = 0; }
+    const int nsteps = (B + 1 + 7) >> 3;                          // 8 blocks (128 columns) per step
+    const int wmax = (w - 20 + 8) >> 2;                           // last word index any valid position needs (x + 8 <= w - 12)
+    for (int i0 = 0; i0 < nsteps; i0 += 4) {
+        uint32_t v[4][7];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int wi = 32 * (i0 + u) + lane;                  // word of columns 4 wi .. 4 wi + 3; this lane's positions start at 4 wi + 3
+            const bool ok = (i0 + u) < nsteps && 4 * wi + 3 <= w - 20;
+            const int a = ok ? wi : 0;
+            v[u][0] = __ldg(rc + a); v[u][1] = __ldg(rc + min(a + 1, wmax)); v[u][2] = __ldg(rc + min(a + 2, wmax));
+            v[u][3] = __ldg(rn + a); v[u][4] = __ldg(rn + min(a + 1, wmax));
+            v[u][5] = __ldg(rs + a); v[u][6] = __ldg(rs + min(a + 1, wmax));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (i0 + u >= nsteps) break;
+            const int x = 4 * (32 * (i0 + u) + lane) + 3;
+            uint32_t any = xend_pass4(v[u][0], v[u][1], v[u][2], v[u][3], v[u][4], v[u][5], v[u][6], thresh);
+            // positions beyond column w - 20 belong to no block the walk looks at
+            const int nvalid = min(max(w - 20 - x + 1, 0), 4);
+            any &= (1u << nvalid) - 1u;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, any != 0u);
+            const uint32_t blk = __ballot_sync(0xFFFFFFFFu, lane < 8 && ((bal >> (4 * lane)) & 0xFu) != 0u) & 0xFFu;
+            if (lane == 0) {
+                const int i = i0 + u;                              // blocks 8 i .. 8 i + 7
+                uint32_t* wp = &sbits[wid][i >> 2];
+                if ((i & 3) == 0) *wp = blk; else *wp |= blk << (8 * (i & 3));
+            }
+        }
     }
+    __syncwarp();
     if (lane == 0) {
-        if (i & 15) sbits[wid][i >> 4] = acc;
         int b = 0;
         while (b < B) {
             const bool lo = (sbits[wid][b >> 5] >> (b & 31)) & 1u, hi = (sbits[wid][(b + 1) >> 5] >> ((b + 1) & 31)) & 1u;

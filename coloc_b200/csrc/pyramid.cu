@@ -26,9 +26,9 @@
 
 namespace clb {
 
-static constexpr int RZ_TW = 64, RZ_TH = 16;          // output tile: 32 lanes x 2 px, 4 warps x 4 rows
+static constexpr int RZ_TW = 64, RZ_TH = 32;          // output tile: 32 lanes x 2 px, 4 warps x 8 rows
 static constexpr int RZ_THREADS = 128;
-static constexpr int RZ_MAX_BOX = 256 * 64;           // staged bytes per tile at most (level 7: 256 x 57)
+static constexpr int RZ_MAX_BOX = 256 * 120;          // staged bytes per tile at most (level 7: 256 x 115)
 
 //   unorm8       RN(v / 255.f) for v in 0..255 as q = v*r, q' = fma(fma(-255, q, v), r, q) with r = RN(1/255): one Newton
 //                correction is exactly the correctly rounded quotient for all 256 inputs (checked exhaustively in exact
@@ -71,6 +71,7 @@ resize_levels_kernel(const LevelTable lt, const ResizePlan rp, const __grid_cons
                      uint32_t* __restrict__ clear, int clear_words) {
     extern __shared__ __align__(128) uint8_t rz_smem[];
     __shared__ __align__(8) uint64_t bar;
+    __shared__ __align__(16) uint4 rowterm[RZ_TH];      // per output row of the tile: {row offset, +1-row offset, wty, 1 - wty}
 
     // nothing below may run before the grid in front has finished: level 0 comes from it, and on the first frame of a geometry
     // so do the column / row tables (resize_tables_kernel) -- every thread waits, not only the one that issues the TMA copy
@@ -78,19 +79,15 @@ resize_levels_kernel(const LevelTable lt, const ResizePlan rp, const __grid_cons
     // the FAST stage's row counters and tile bitmap start every frame at zero (no kernel of this frame has touched them yet)
     for (int i = blockIdx.x * RZ_THREADS + threadIdx.x; i < clear_words; i += gridDim.x * RZ_THREADS) clear[i] = 0u;
 
-    // which level / tile does this CTA own?
-    int tile = blockIdx.x, L = 1, tx_n = 0;
-    for (; L < lt.n; ++L) {
-        tx_n = (lt.w[L] + rp.tile_w[L] - 1) / rp.tile_w[L];
-        const int cnt = tx_n * ((lt.h[L] + rp.tile_h[L] - 1) / rp.tile_h[L]);
-        if (tile < cnt) break;
-        tile -= cnt;
-    }
-    if (L >= lt.n) return;
+    // which level / tile does this CTA own?  (host-computed bases and an exact multiply-shift division: no divisions here)
+    int L = 1;
+    while (L + 1 < lt.n && (int)blockIdx.x >= rp.tile_base[L + 1]) ++L;
+    const int tile = blockIdx.x - rp.tile_base[L];
+    const int tyi = rp.tiles_x[L] == 1 ? tile : (int)__umulhi((uint32_t)tile, rp.tiles_x_magic[L]), txi = tile - tyi * rp.tiles_x[L];
     const int dw = lt.w[L], dh = lt.h[L], ds = lt.stride[L];
     uint8_t* __restrict__ dst = const_cast<uint8_t*>(lt.img[L]);
-    const int tw = rp.tile_w[L], th = rp.tile_h[L];              // 64 x 16 unless the level's scale makes that footprint too large
-    const int tx0 = (tile % tx_n) * tw, ty0 = (tile / tx_n) * th;
+    const int tw = rp.tile_w[L], th = rp.tile_h[L];              // 64 x 32 unless the level's scale makes that footprint too large
+    const int tx0 = txi * tw, ty0 = tyi * th;
     const int bw = rp.box_w[L], bh = rp.box_h[L];
     const uint2* __restrict__ ctab = rp.tab + rp.col_off[L];
     const uint2* __restrict__ rtab = rp.tab + rp.row_off[L];
@@ -104,10 +101,17 @@ resize_levels_kernel(const LevelTable lt, const ResizePlan rp, const __grid_cons
         ptx_tma_load_2d(rz_smem, &maps.resize[L], bx0, by0, &bar);      // rz_smem[r][j] = level0[by0 + r][bx0 + j]
     }
     ptx_grid_dep_launch();
+    if (threadIdx.x < RZ_TH) {
+        const int y = min(ty0 + (int)threadIdx.x, dh - 1);
+        const uint2 re = __ldg(&rtab[y]);
+        const uint32_t r0 = ((re.x & 0x7FFFFFFFu) - (uint32_t)by0) * (uint32_t)bw;
+        const float wty = __uint_as_float(re.y);
+        rowterm[threadIdx.x] = make_uint4(r0, r0 + ((re.x >> 31) ? 0u : (uint32_t)bw), re.y, __float_as_uint(__fsub_rn(1.0f, wty)));
+    }
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = tx0 + 2 * lane;                 // this thread's two columns x, x + 1
-    const int yb = ty0 + 4 * warp;                // and four rows
+    constexpr int RPW = RZ_TH / (RZ_THREADS / 32);   // rows per warp
     // column terms: box-relative offsets of the texel pair (the +1 neighbour collapses onto the origin at the right edge), weights
     uint32_t c0[2], c1[2];
     float wtx[2];
@@ -120,18 +124,19 @@ resize_levels_kernel(const LevelTable lt, const ResizePlan rp, const __grid_cons
     }
     const float2 wx = make_float2(wtx[0], wtx[1]);
     const float2 ix = __fadd2_rn(make_float2(1.0f, 1.0f), make_float2(-wtx[0], -wtx[1]));
-    __syncthreads();                              // barrier initialised
+    __syncthreads();                              // barrier initialised, row terms written
     ptx_mbar_wait(&bar, 0);
 
     if (x >= dw || 2 * lane >= tw) return;
-#pragma unroll
-    for (int rr = 0; rr < 4; ++rr) {
-        const int y = yb + rr;
-        if (y >= dh || 4 * warp + rr >= th) break;
-        const uint2 re = __ldg(&rtab[y]);
-        const uint8_t* r0 = rz_smem + ((re.x & 0x7FFFFFFFu) - (uint32_t)by0) * (uint32_t)bw;
-        const uint8_t* r1 = r0 + ((re.x >> 31) ? 0 : bw);
-        const float wty = __uint_as_float(re.y), ivy = __fsub_rn(1.0f, wty);
+    const bool pair = x + 1 < dw && 2 * lane + 1 < tw;
+    const int rows = min(min(RPW, th - RPW * warp), dh - (ty0 + RPW * warp));
+    uint8_t* o = dst + (size_t)(ty0 + RPW * warp) * ds + x;
+#pragma unroll 2
+    for (int rr = 0; rr < rows; ++rr, o += ds) {
+        const uint4 rt = rowterm[RPW * warp + rr];
+        const uint8_t* r0 = rz_smem + rt.x;
+        const uint8_t* r1 = rz_smem + rt.y;
+        const float wty = __uint_as_float(rt.z), ivy = __uint_as_float(rt.w);
         const uint32_t bias = 0x4B000000u;
         const float2 p00 = unorm8x2(bias | r0[c0[0]], bias | r0[c0[1]]);
         const float2 p10 = unorm8x2(bias | r0[c1[0]], bias | r0[c1[1]]);
@@ -142,10 +147,9 @@ resize_levels_kernel(const LevelTable lt, const ResizePlan rp, const __grid_cons
         const float2 v = __ffma2_rn(make_float2(ivy, ivy), xa, __fmul2_rn(make_float2(wty, wty), xb));
         const float2 res = __ffma2_rn(v, make_float2(255.0f, 255.0f), make_float2(0.5f, 0.5f));
         const float2 fl = __fadd2_rd(res, make_float2(8388608.0f, 8388608.0f));        // res in [0.5, 255.5]: trunc = floor
-        const uint32_t b0 = __float_as_uint(fl.x) & 0xFFu, b1 = __float_as_uint(fl.y) & 0xFFu;
-        uint8_t* o = dst + (size_t)y * ds + x;
-        if (x + 1 < dw && 2 * lane + 1 < tw) *reinterpret_cast<uint16_t*>(o) = (uint16_t)(b0 | (b1 << 8));   // x is even, rows are 128-B aligned
-        else *o = (uint8_t)b0;
+        const uint32_t b01 = __byte_perm(__float_as_uint(fl.x), __float_as_uint(fl.y), 0x7740);   // byte 0 of each
+        if (pair) *reinterpret_cast<uint16_t*>(o) = (uint16_t)b01;      // x is even, rows are 128-B aligned
+        else *o = (uint8_t)b01;
     }
 }
 
@@ -160,7 +164,8 @@ size_t resize_table_entries(const LevelTable& lt) {
 // tile shrinks on levels whose scale would push that past what one TMA box (256 wide) or the staging buffer holds.
 int resize_plan(const LevelTable& lt, ResizePlan& rp) {
     int off = 0;
-    for (int L = 0; L < CLB_MAX_LEVELS; ++L) { rp.box_w[L] = rp.box_h[L] = 16; rp.col_off[L] = rp.row_off[L] = 0; rp.tile_w[L] = RZ_TW; rp.tile_h[L] = RZ_TH; }
+    for (int L = 0; L < CLB_MAX_LEVELS; ++L) { rp.box_w[L] = rp.box_h[L] = 16; rp.col_off[L] = rp.row_off[L] = 0; rp.tile_w[L] = RZ_TW; rp.tile_h[L] = RZ_TH; rp.tiles_x[L] = 1; rp.tiles_x_magic[L] = 0xFFFFFFFFu; }
+    for (int L = 0; L <= CLB_MAX_LEVELS; ++L) rp.tile_base[L] = 0;
     for (int L = 1; L < lt.n; ++L) {
         const double f = lt.f[L];
         int tw = RZ_TW, th = RZ_TH;
@@ -173,6 +178,15 @@ int resize_plan(const LevelTable& lt, ResizePlan& rp) {
         }
         rp.tile_w[L] = tw; rp.tile_h[L] = th;
         rp.box_w[L] = bw; rp.box_h[L] = bh;
+        // tile index -> (row, column) of the level's tile grid by multiply-shift, checked exhaustively here
+        const int txn = lt.w[L] > 0 ? (lt.w[L] + tw - 1) / tw : 1, tyn = lt.h[L] > 0 ? (lt.h[L] + th - 1) / th : 0;
+        const uint32_t magic = txn == 1 ? 0xFFFFFFFFu : (uint32_t)(0x100000000ull / (uint64_t)txn) + 1u;
+        for (long long t = 0; t < (long long)txn * tyn; ++t) {
+            const uint32_t q = txn == 1 ? (uint32_t)t : (uint32_t)(((uint64_t)t * magic) >> 32);
+            if (q != (uint32_t)(t / txn)) { snprintf(g_err, sizeof(g_err), "pyramid level %d: tile grid %d x %d is too large for the tile decode", L, txn, tyn); return CLB_EUNSUPPORTED; }
+        }
+        rp.tiles_x[L] = txn; rp.tiles_x_magic[L] = magic;
+        rp.tile_base[L + 1] = rp.tile_base[L] + txn * tyn;
         rp.col_off[L] = off; off += lt.w[L];
         rp.row_off[L] = off; off += lt.h[L];
     }
@@ -189,10 +203,9 @@ int launch_resize_tables(const LevelTable& lt, const ResizePlan& rp, uint2* d_ta
 }
 
 int launch_resize(const LevelTable& lt, const ResizePlan& rp, const LevelMaps& maps, uint32_t* clear, int clear_words, cudaStream_t s, bool pdl) {
-    int tiles = 0, smem = 0;
+    int smem = 0;
+    const int tiles = lt.n > 1 ? rp.tile_base[lt.n] : 0;
     for (int L = 1; L < lt.n; ++L) {
-        if (lt.w[L] < 1 || lt.h[L] < 1) continue;
-        tiles += ((lt.w[L] + rp.tile_w[L] - 1) / rp.tile_w[L]) * ((lt.h[L] + rp.tile_h[L] - 1) / rp.tile_h[L]);
         const int need = (rp.box_w[L] * rp.box_h[L] + 127) & ~127;
         smem = need > smem ? need : smem;
     }

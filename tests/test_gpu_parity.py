@@ -442,6 +442,34 @@ def test_config5_frame_end_to_end(clb, oracle):
     det.close()
 
 
+def test_alternating_frames_reuse_buffers(clb, oracle):
+    """One detector, one geometry, DIFFERENT frame contents back to back (the pyramid, score map and keypoint buffers are
+    reused with new contents; the frame's kernels are a programmatic-dependent-launch chain): every frame equals the oracle.
+    Catches a consumer kernel that reads a previous frame's data out of a non-coherent cache."""
+    w, h = 640, 480
+    frames = [synth.config_frame(w, h, k) for k in range(3)] + [synth.textured_frame(w, h, 77)]
+    want = [oracle.detect_describe(f, cap=50000) for f in frames]
+    det = clb.Detector(w, h, maxkp=50000)
+    for it in range(3):
+        for f, (okps, odesc) in zip(frames, want):
+            kps, desc = det.detect_and_describe(f)
+            assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc, odesc), it
+    det.close()
+    fs = clb.FrameStream(w, h, depth=2, maxkp=50000)
+    order = [0, 1, 2, 3, 3, 1, 0, 2, 2, 0]
+    got = []
+    for i, k in enumerate(order):
+        if fs.in_flight() == 2:
+            got.append(fs.next()[:3])
+        fs.submit(frames[k], tag=i)
+    while fs.in_flight():
+        got.append(fs.next()[:3])
+    for tag, kps, desc in got:
+        okps, odesc = want[order[tag]]
+        assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc, odesc), tag
+    fs.close()
+
+
 def test_golden_frame(clb):
     g = np.load(os.path.join(GOLD, "frame168.npz"))
     det = clb.Detector(168, 126, maxkp=5000, thresh=int(g["thresh"]))

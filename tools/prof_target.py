@@ -21,7 +21,7 @@ if what in ("match", "matchfull"):
     torch.cuda.synchronize()
 else:
     w, h = (3840, 2160) if what == "detect4k" else (1280, 720)
-    img = synth.textured_frame(w, h, 1000)
+    img = synth.config_frame(w, h, 0)
     det = clb.Detector(w, h, maxkp=400000)
     for _ in range(4):
         k, d = det.detect_and_describe(img)
