@@ -121,6 +121,34 @@ def microbench_mma(device=0):
     return dict(zip(k, [float(v) for v in out]))
 
 
+class PinnedArray:
+    """numpy view of page-locked host memory from clb_host_alloc (freed with the object)"""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * self.dtype.itemsize
+        self._p = C.c_void_p()
+        lib().clb_host_alloc.argtypes = [C.c_size_t, C.c_void_p]
+        _check(lib().clb_host_alloc(max(n, 64), C.byref(self._p)))
+        buf = (C.c_uint8 * max(n, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def __del__(self):
+        try:
+            if self._p:
+                lib().clb_host_free.argtypes = [C.c_void_p]
+                lib().clb_host_free(self._p); self._p = C.c_void_p()
+        except Exception:
+            pass
+
+
+def pinned_like(a):
+    """a page-locked copy of a numpy array (returns (holder, array): keep the holder alive)"""
+    h = PinnedArray(a.shape, a.dtype)
+    h.array[...] = a
+    return h, h.array
+
+
 def _sarg(stream):
     """cudaStream_t argument: None -> NULL (= the object's own stream); a torch stream handle of 0 (the legacy
     default stream) is passed as cudaStreamLegacy (0x1) so that it is not mistaken for NULL."""
@@ -174,13 +202,19 @@ class Detector:
         _check(lib().clb_detector_level_dims(self._h, w, h, _ptr(ws), _ptr(hs), _ptr(fs)))
         return ws.tolist(), hs.tolist(), fs
 
-    def detect_and_describe(self, img, cap=None, copy=True):
-        """GPUDetector::detectAndDescribe (GPUDetector.hpp:216-291) on a host uint8 image."""
+    def detect_and_describe(self, img, cap=None, copy=True, pinned=False):
+        """GPUDetector::detectAndDescribe (GPUDetector.hpp:216-291) on a host uint8 image.  pinned=True keeps the output
+        buffers in page-locked memory: the describe kernel then writes the descriptors straight into them."""
         img = np.ascontiguousarray(img, np.uint8)
         h, w = img.shape
         cap = cap if cap is not None else self.opts.maxkp
-        if getattr(self, "_cap", -1) != cap:      # output buffers are kept across calls (no 10 MB allocation + zero fill per frame)
-            self._kbuf = np.empty(cap, KP_DTYPE); self._dbuf = np.empty((cap, 8), np.uint64); self._cap = cap
+        if getattr(self, "_cap", -1) != cap or getattr(self, "_pinned", False) != pinned:      # output buffers are kept across calls
+            if pinned:
+                self._kh = PinnedArray((cap,), KP_DTYPE); self._dh = PinnedArray((cap, 8), np.uint64)
+                self._kbuf, self._dbuf = self._kh.array, self._dh.array
+            else:
+                self._kbuf = np.empty(cap, KP_DTYPE); self._dbuf = np.empty((cap, 8), np.uint64)
+            self._cap = cap; self._pinned = pinned
         n = C.c_int(0)
         _check(lib().clb_detect_describe(self._h, _ptr(img), w, h, img.strides[0], _ptr(self._kbuf), _ptr(self._dbuf), cap, C.byref(n)))
         # like the reference's public `kps` / `desc` members these hold the LAST frame: copy=False hands out views that the next call overwrites

@@ -46,7 +46,7 @@ struct clb_detector {
     int tex_w, tex_h, tex_n;
     bool tex_fresh;      // texture objects created since the last describe launch: that launch must be a plain one (see run_pipeline)
     cudaStream_t copy_stream;   // keypoint D2H of the blocking per-frame call, behind the describe kernel
-    cudaEvent_t ev_count, ev_fast;
+    cudaEvent_t ev_count, ev_fast, ev_done;
     bool copy_ready;
     // per frame geometry (rebuilt when w x h changes): TMA tensor maps of the levels, the resize kernel's source-box plan and
     // its column / row tables
@@ -229,6 +229,13 @@ int clb_microbench_pipes(int device, double* out8) {
     return microbench_pipes(out8);
 }
 
+int clb_host_alloc(size_t bytes, void** out) {
+    if (!out || bytes == 0) return CLB_EINVAL;
+    CLB_CUDA(cudaMallocHost(out, bytes));
+    return CLB_OK;
+}
+void clb_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 int clb_microbench_mma(int device, double* out6) {
     if (!out6) return CLB_EINVAL;
     CLB_CUDA(cudaSetDevice(device));
@@ -270,7 +277,7 @@ void clb_detector_destroy(clb_detector* d) {
     destroy_level_textures(d->tex, d->tex_n);
     d->pyr.release(); d->fast_scratch.release(); d->kps.release(); d->desc.release(); d->misc.release(); d->stage.release(); d->rtab.release();
     if (d->h_total) cudaFreeHost(d->h_total);
-    if (d->copy_ready) { cudaEventDestroy(d->ev_count); cudaEventDestroy(d->ev_fast); cudaStreamDestroy(d->copy_stream); }
+    if (d->copy_ready) { cudaEventDestroy(d->ev_count); cudaEventDestroy(d->ev_fast); cudaEventDestroy(d->ev_done); cudaStreamDestroy(d->copy_stream); }
     if (d->stream) cudaStreamDestroy(d->stream);
     delete d;
 }
@@ -292,6 +299,16 @@ int clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, in
     float tmp[CLB_MAX_LEVELS];
     level_dims(d->o, w, h, ws, hs, fs ? fs : tmp);
     return CLB_OK;
+}
+
+// the blocking per-frame call waits by polling the event: a sleeping wait (cudaEventSynchronize / cudaStreamSynchronize) is
+// woken 10-20 us late, a visible share of a 0.13 - 0.3 ms call; the reference's caller blocks here as well (GPUDetector.hpp:290)
+static int spin_wait(cudaEvent_t ev) {
+    for (;;) {
+        const cudaError_t e = cudaEventQuery(ev);
+        if (e == cudaSuccess) return CLB_OK;
+        if (e != cudaErrorNotReady) return set_cuda_error(e, "cudaEventQuery", __FILE__, __LINE__);
+    }
 }
 
 static int check_frame(clb_detector* d, int w, int h, int stride) {
@@ -357,6 +374,7 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
         CLB_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
         CLB_CUDA(cudaEventCreateWithFlags(&d->ev_count, cudaEventDisableTiming));
         CLB_CUDA(cudaEventCreateWithFlags(&d->ev_fast, cudaEventDisableTiming));
+        CLB_CUDA(cudaEventCreateWithFlags(&d->ev_done, cudaEventDisableTiming));
         d->copy_ready = true;
     }
     // the keypoints are final after the FAST stage: their count comes back on a second stream while the describe kernel runs
@@ -370,12 +388,25 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
     rc = launch_fast(lt, d->maps, d->o.thresh, d->fast_quirk, d->fast_scratch.p, d->fast_scratch.cap, d->kps.as<clb_keypoint>(), d->o.maxkp, d_total, s, true, false);
     if (rc) return rc;
     CLB_CUDA(cudaEventRecord(d->ev_fast, s));
-    rc = launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, d->o.maxkp, d->desc.as<uint64_t>(), s, &d->tex, describe_pdl(d));
+    // a pinned (page-locked) descriptor buffer is written by the describe kernel itself, row by row over PCIe while it runs:
+    // the 64 n-byte D2H copy behind the kernel disappears from the call's latency.  Pageable buffers take the copy.
+    uint64_t* desc_dev = d->desc.as<uint64_t>();
+    bool desc_direct = false;
+    if (desc_out && cap > 0) {
+        cudaPointerAttributes pa;
+        if (cudaPointerGetAttributes(&pa, desc_out) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer) {
+            desc_dev = static_cast<uint64_t*>(pa.devicePointer); desc_direct = true;
+        }
+        cudaGetLastError();
+    }
+    rc = launch_describe(lt, d->kps.as<clb_keypoint>(), 0, d_total, desc_direct ? (cap < d->o.maxkp ? cap : d->o.maxkp) : d->o.maxkp, desc_dev, s, &d->tex, describe_pdl(d));
     if (rc) return rc;
+    CLB_CUDA(cudaEventRecord(d->ev_done, s));
     CLB_CUDA(cudaStreamWaitEvent(d->copy_stream, d->ev_fast, 0));
     CLB_CUDA(cudaMemcpyAsync(d->h_total, d_total, sizeof(int), cudaMemcpyDeviceToHost, d->copy_stream));
     CLB_CUDA(cudaEventRecord(d->ev_count, d->copy_stream));
-    CLB_CUDA(cudaEventSynchronize(d->ev_count));
+    rc = spin_wait(d->ev_count);
+    if (rc) return rc;
     const int n = *d->h_total;
     *n_out = n;
     if (n > d->o.maxkp || n > cap) {
@@ -384,12 +415,17 @@ int clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int 
         return CLB_ECAPACITY;
     }
     if (n > 0) {
-        if (kps_out) CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, d->copy_stream));
-        if (desc_out) CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
-        if (kps_out) CLB_CUDA(cudaStreamSynchronize(d->copy_stream));
+        if (kps_out) {
+            CLB_CUDA(cudaMemcpyAsync(kps_out, d->kps.p, (size_t)n * sizeof(clb_keypoint), cudaMemcpyDeviceToHost, d->copy_stream));
+            CLB_CUDA(cudaEventRecord(d->ev_count, d->copy_stream));
+        }
+        if (desc_out && !desc_direct) {
+            CLB_CUDA(cudaMemcpyAsync(desc_out, d->desc.p, (size_t)n * 64, cudaMemcpyDeviceToHost, s));
+            CLB_CUDA(cudaEventRecord(d->ev_done, s));
+        }
+        if (kps_out) { rc = spin_wait(d->ev_count); if (rc) return rc; }
     }
-    CLB_CUDA(cudaStreamSynchronize(s));
-    return CLB_OK;
+    return spin_wait(d->ev_done);
 }
 
 int clb_pyramid(clb_detector* d, const uint8_t* gray, int w, int h, int stride, uint8_t* levels_out) {

@@ -15,6 +15,7 @@
 #ifndef COLOC_B200_H
 #define COLOC_B200_H
 #include <stdint.h>
+#include <stddef.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -96,6 +97,11 @@ int  clb_detector_level_dims(const clb_detector* d, int w, int h, int32_t* ws, i
  * `cap` (or maxkp) keypoints returns CLB_ECAPACITY with *n_out = needed. */
 int  clb_detect_describe(clb_detector* d, const uint8_t* gray, int w, int h, int stride,
                          clb_keypoint* kps_out, uint64_t* desc_out, int cap, int* n_out);
+/* page-locked host memory for callers that want the copies of the calls above to overlap the kernels (any cudaMallocHost /
+ * cudaHostRegister memory works the same).  With a page-locked desc_out, clb_detect_describe lets the describe kernel write
+ * the descriptors straight into it while it runs (no D2H copy behind the kernel); a page-locked gray is DMA-ed from directly. */
+int  clb_host_alloc(size_t bytes, void** out);
+void clb_host_free(void* p);
 /* same with a DEVICE image; results stay on the device (d_kps / d_desc owned by the detector,
  * valid until the next call); *n_out is read back (one 4-byte D2H + stream sync). */
 int  clb_detect_describe_dev(clb_detector* d, const uint8_t* d_gray, int w, int h, int stride,

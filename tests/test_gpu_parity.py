@@ -470,6 +470,27 @@ def test_alternating_frames_reuse_buffers(clb, oracle):
     fs.close()
 
 
+def test_pinned_outputs_written_by_the_kernel(clb, oracle):
+    """page-locked descriptor buffer: the describe kernel writes it directly (no D2H copy); same bytes as the copy path, the
+    capacity error still reports the needed count and nothing is written beyond `cap` rows"""
+    w, h = 640, 480
+    img = synth.config_frame(w, h, 2)
+    okps, odesc = oracle.detect_describe(img, cap=50000)
+    hold, pimg = clb.pinned_like(img)
+    det = clb.Detector(w, h, maxkp=50000)
+    for it in range(3):
+        kps, desc = det.detect_and_describe(pimg, pinned=True)
+        assert np.array_equal(kps.view(np.uint8), okps.view(np.uint8)) and np.array_equal(desc, odesc)
+    small = len(okps) - 100
+    det._dbuf[small:] = np.uint64(0x5555555555555555)
+    with pytest.raises(clb.ClbError) as e:
+        det.detect_and_describe(pimg, cap=None, pinned=True) if False else clb.api._check(clb.lib().clb_detect_describe(
+            det._h, clb.api._ptr(pimg), w, h, w, clb.api._ptr(det._kbuf), clb.api._ptr(det._dbuf), small, __import__("ctypes").byref(__import__("ctypes").c_int(0))))
+    assert e.value.code == 3
+    assert (det._dbuf[small:] == np.uint64(0x5555555555555555)).all()
+    det.close()
+
+
 def test_golden_frame(clb):
     g = np.load(os.path.join(GOLD, "frame168.npz"))
     det = clb.Detector(168, 126, maxkp=5000, thresh=int(g["thresh"]))

@@ -17,7 +17,8 @@ for (w, h) in ((640, 480), (1280, 720), (3840, 2160)):
     t = np.min(np.array(ts[2:]), axis=0) * 1e3
     clb.set_timing(False)
     lat = []
+    det.detect_and_describe(img, copy=False, pinned=True)
     for _ in range(30):
-        t0 = time.perf_counter(); det.detect_and_describe(img, copy=False); lat.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); det.detect_and_describe(img, copy=False, pinned=True); lat.append(time.perf_counter() - t0)
     print(f"{w}x{h}: {len(k)} kp  resize {t[0]:.1f} us  fast {t[1]:.1f} us  describe {t[2]:.1f} us  sum {t.sum():.1f} us; blocking call {1e6 * np.median(lat):.0f} us (min {1e6 * min(lat):.0f})", flush=True)
     det.close()
