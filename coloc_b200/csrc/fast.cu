@@ -82,13 +82,13 @@ __device__ __forceinline__ uint32_t xend_pass4(uint32_t w0, uint32_t w1, uint32_
     return any;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int thresh, int* __restrict__ xend) {
-    __shared__ uint32_t sbits[8][FQ_WORDS];
+    __shared__ uint32_t sbits[4][FQ_WORDS];
     ptx_grid_dep_wait();                // every CTA: the level comes from the resize kernel, and the score kernel behind this
     ptx_grid_dep_launch();              // one relies on this grid not finishing before that one has
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qrow = blockIdx.x * 8 + wid;
+    const int qrow = blockIdx.x * 4 + wid;
     if (qrow >= qr.row_base[qr.n]) return;
     int k = 0;
     while (k + 1 < qr.n && qrow >= qr.row_base[k + 1]) ++k;
@@ -103,10 +103,11 @@ fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int t
     const int B = (w - 38) >> 4;                                  // blocks 0..B are looked at: columns 3 .. w - 20
     const int nsteps = (B + 1 + 7) >> 3;                          // 8 blocks (128 columns) per step
     const int wmax = (w - 20 + 8) >> 2;                           // last word index any valid position needs (x + 8 <= w - 12)
-    for (int i0 = 0; i0 < nsteps; i0 += 4) {
-        uint32_t v[4][7];
+    constexpr int XU = 10;                                        // steps whose loads are in flight together (1286 px = 10 steps)
+    for (int i0 = 0; i0 < nsteps; i0 += XU) {
+        uint32_t v[XU][7];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < XU; ++u) {
             const int wi = 32 * (i0 + u) + lane;                  // word of columns 4 wi .. 4 wi + 3; this lane's positions start at 4 wi + 3
             const bool ok = (i0 + u) < nsteps && 4 * wi + 3 <= w - 20;
             const int a = ok ? wi : 0;
@@ -115,7 +116,7 @@ fast_xend_kernel(const LevelTable lt, const RowMap rm, const QuirkRows qr, int t
             v[u][5] = __ldg(rs + a); v[u][6] = __ldg(rs + min(a + 1, wmax));
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < XU; ++u) {
             if (i0 + u >= nsteps) break;
             const int x = 4 * (32 * (i0 + u) + lane) + 3;
             uint32_t any = xend_pass4(v[u][0], v[u][1], v[u][2], v[u][3], v[u][4], v[u][5], v[u][6], thresh);
@@ -261,7 +262,7 @@ fast_nms_kernel(const LevelTable lt, const RowMap rm, int thresh, uint8_t* __res
         keep = keep && inside;
         if (inside) map[(size_t)(grow0 + gy) * lt.stride[0] + gx] = keep ? (uint8_t)s : (uint8_t)0;
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
-        if ((tid & 31) == 0 && bal) atomicAdd(&row_count[grow0 + gy], __popc(bal));
+        if ((tid & 31) == 0 && bal) { atomicAdd(&row_count[grow0 + gy], __popc(bal)); atomicAdd(&row_count[rm.row_base[rm.n] + ((grow0 + gy) >> 6)], __popc(bal)); }
     }
 }
 
@@ -504,21 +505,25 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ L
         // word of the staged pixels; east / west neighbours come from the adjacent words by byte permute.
         //   bright > p + t  <=>  bright + ~p - t      has its lane's sign bit clear   (~p = -p - 1 in a 16-bit lane)
         //   dark   < p - t  <=>  dark   + ~p + t + 1  has its lane's sign bit set
-        constexpr int WPR = 18, NITEM = F::CH * WPR;
+        // Thread -> (word column wq = tid % 18, row tid / 18): a pass covers 14 rows and only the row changes between passes,
+        // so the column terms (first valid position, staged-pixel address) are computed once per thread (the first version
+        // re-derived (row, column) from a flat item index with a division per pass: 30 of its 110 instructions per item).
+        constexpr int WPR = 18, RPP = 256 / WPR, NPASS = (F::CH + RPP - 1) / RPP;
         const uint32_t k_b = ((uint32_t)(-thresh) & 0xFFFFu) * 0x10001u, k_d = ((uint32_t)(thresh + 1) & 0xFFFFu) * 0x10001u;
         const int xlo = max(3, x0 - 1);                                        // valid gx range of this tile's score region: [xlo, xhi)
-        for (int base = 0; base < NITEM; base += 256) {
-            const int it = base + tid;
+        const int wq = tid % WPR, rr = tid / WPR;
+        const int c0 = 4 * wq - 3, gxb = x0 - 1 + c0;
+        const uint32_t lowmask = 0xFu << min(max(xlo - gxb, 0), 4);
+        const int xcap = x0 + F::CW - 1 - gxb;
+        const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+        for (int p = 0; p < NPASS; ++p) {
+            const int r = rr + RPP * p;
             uint32_t cm = 0;
-            int r = 0, c0 = 0;
-            if (it < NITEM) {
-                r = it / WPR;
-                const int wq = it - r * WPR;
-                c0 = 4 * wq - 3;
-                const int gy = y0 - 1 + r, gxb = x0 - 1 + c0;
-                const int xhi = min(s_xlim[r], x0 + F::CW - 1);
-                const int nlow = min(max(xlo - gxb, 0), 4), nval = min(max(xhi - gxb, 0), 4);
-                const uint32_t vmask = (0xFu << nlow) & ((1u << nval) - 1u);
+            if (rr < RPP && r < F::CH) {
+                const int gy = y0 - 1 + r;
+                const int nval = min(max(min(s_xlim[r] - gxb, xcap), 0), 4);
+                const uint32_t vmask = lowmask & ((1u << nval) - 1u);
                 if (gy >= 3 && gy < h - 3 && vmask) {
                     const uint32_t* wp = reinterpret_cast<const uint32_t*>(&px[(r + 3) * F::SSTR + (F::XO - 4) + 4 * wq]);
                     const uint32_t cw = wp[0], cl = wp[-1], cr = wp[1];
@@ -541,15 +546,16 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ L
                     cm = (t2 | (t2 >> 14)) & vmask;
                 }
             }
-            if (__ballot_sync(0xFFFFFFFFu, cm != 0u)) {
-                const uint32_t cnt = __popc(cm);
-                uint32_t pre = cnt;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, pre, o); if (lane >= o) pre += t; }
+            // queue slots: a lane has 0..4 candidates; the warp prefix of such small counts is three ballots (one per bit of
+            // the count) and six population counts instead of a five-step shuffle scan
+            const uint32_t cnt = __popc(cm);
+            const uint32_t b0 = __ballot_sync(0xFFFFFFFFu, cnt & 1u), b1 = __ballot_sync(0xFFFFFFFFu, cnt & 2u), b2 = __ballot_sync(0xFFFFFFFFu, cnt & 4u);
+            const int total = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+            if (total) {
                 int b = 0;
-                if (lane == 31) b = atomicAdd(&n1, (int)pre);
-                b = __shfl_sync(0xFFFFFFFFu, b, 31);
-                int pos = b + (int)(pre - cnt);
+                if (lane == 0) b = atomicAdd(&n1, total);
+                b = __shfl_sync(0xFFFFFFFFu, b, 0);
+                int pos = b + __popc(b0 & lt_mask) + 2 * __popc(b1 & lt_mask) + 4 * __popc(b2 & lt_mask);
                 const int i0 = r * F::CW + c0;
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
@@ -683,6 +689,18 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ L
         const int tx = tile % tx_n;          // which 64-px tiles of a row hold keypoints: the tail only visits those
         if (bitmap) atomicOr(&bitmap[(size_t)(grow0 + y0 + tid) * rm.bm_words + (tx >> 5)], 1u << (tx & 31));
     }
+    if (tid < 32 && TH <= 32) {
+        // keypoints per chunk of 64 global rows (stored behind the row counters): the tail's row offsets then cost two loads per
+        // thread instead of a sum over every earlier row.  A tile's rows lie in at most two chunks.
+        const int grow = grow0 + y0 + tid;
+        const int c = tid < TH ? rowcnt[tid] : 0;
+        const int first = (grow0 + y0) >> 6;
+        int a = (grow >> 6) == first ? c : 0, b = c - a;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { a += __shfl_xor_sync(0xFFFFFFFFu, a, o); b += __shfl_xor_sync(0xFFFFFFFFu, b, o); }
+        if (tid == 0 && a) atomicAdd(&row_count[rm.row_base[rm.n] + first], a);
+        if (tid == 1 && b) atomicAdd(&row_count[rm.row_base[rm.n] + first + 1], b);
+    }
 }
 
 // v2 tail: row offsets (sum of the counts of all earlier rows, computed by every block for itself -- a few
@@ -698,11 +716,15 @@ compact2_kernel(const LevelTable lt, const RowMap rm, const uint8_t* __restrict_
     const int grow0 = blockIdx.x * 8, grow = grow0 + wid;
     ptx_grid_dep_wait();                // the score map, row counts and tile bitmap of the kernel in front
     ptx_grid_dep_launch();
+    // keypoints in front of this block's rows = whole chunks of 64 rows (counted by the score kernel) + the rows of the last,
+    // partial chunk
     int acc = 0;
-    for (int i = tid; i < grow0; i += 256) acc += __ldg(row_count + i);
+    const int nchunk = grow0 >> 6;
+    for (int i = tid; i < nchunk; i += 256) acc += __ldcg(row_count + nrows + i);
+    for (int i = (nchunk << 6) + tid; i < grow0; i += 256) acc += __ldcg(row_count + i);
 #pragma unroll
     for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
-    if (lane == 0) { wsum[wid] = acc; rcnt[wid] = grow < nrows ? __ldg(row_count + grow) : 0; }
+    if (lane == 0) { wsum[wid] = acc; rcnt[wid] = grow < nrows ? __ldcg(row_count + grow) : 0; }
     __syncthreads();
     int out = 0;
 #pragma unroll
@@ -808,13 +830,20 @@ static RowMap make_rowmap(const LevelTable& lt) {
 // widths on which the compiled reference's `1 << 32` (KFAST.h:243) can drop a row's last 32 columns
 static inline bool fast_quirk_width(int w) { return w >= 38 && ((w - 38) & 15) == 0; }
 
-// scratch layout: [nms map: total_rows x stride0][row_count][tile bitmap][row_off][xend], the int arrays total_rows long
+// scratch layout: [nms map: total_rows x stride0][row_count: total_rows ints + one per chunk of 64 rows][tile bitmap][row_off][xend]
+struct FastLayout { size_t rows, map_bytes, cnt_bytes, bm_words, bm_bytes; };
+static FastLayout fast_layout(const LevelTable& lt) {
+    FastLayout f; f.rows = 0;
+    for (int i = 0; i < lt.n; ++i) f.rows += lt.h[i];
+    f.map_bytes = (f.rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
+    f.cnt_bytes = ((f.rows + f.rows / 64 + 2) * sizeof(int) + 255) & ~(size_t)255;
+    f.bm_words = ((size_t)(lt.n > 0 ? (lt.w[0] + FT_TW - 1) / FT_TW : 1) + 31) / 32;
+    f.bm_bytes = (f.rows * f.bm_words * 4 + 255) & ~(size_t)255;
+    return f;
+}
 size_t fast_scratch_bytes(const LevelTable& lt) {
-    size_t rows = 0;
-    for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
-    size_t map = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
-    const size_t bm_words = ((size_t)(lt.n > 0 ? (lt.w[0] + FT_TW - 1) / FT_TW : 1) + 31) / 32;
-    return map + 3 * ((rows * sizeof(int) + 255) & ~(size_t)255) + ((rows * bm_words * 4 + 255) & ~(size_t)255) + 256;
+    const FastLayout f = fast_layout(lt);
+    return f.map_bytes + 3 * f.cnt_bytes + f.bm_bytes + 256;
 }
 
 int fast_tile_box(int* w, int* h) { *w = Fast2<32, true>::SSTR; *h = Fast2<32, true>::SH; return CLB_OK; }
@@ -824,13 +853,11 @@ int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int qui
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s, bool pdl, bool standalone) {
     if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
     RowMap rm = make_rowmap(lt);
-    const size_t rows = rm.row_base[lt.n];
-    const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
-    const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
+    const FastLayout lay = fast_layout(lt);
+    const size_t rows = lay.rows, map_bytes = lay.map_bytes, cnt_bytes = lay.cnt_bytes, bm_bytes = lay.bm_bytes;
     uint8_t* nms = reinterpret_cast<uint8_t*>(scratch);
-    // [map][row_count][tile bitmap][row_off][xend]: the counts and the bitmap are cleared together (by the resize kernel)
-    rm.bm_words = (int)((((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32);
-    const size_t bm_bytes = (rows * (size_t)rm.bm_words * 4 + 255) & ~(size_t)255;
+    // [map][row_count + chunk counts][tile bitmap][row_off][xend]: the counts and the bitmap are cleared together (by the resize kernel)
+    rm.bm_words = (int)lay.bm_words;
     int* row_count = reinterpret_cast<int*>(nms + map_bytes);
     uint32_t* bitmap = reinterpret_cast<uint32_t*>(nms + map_bytes + cnt_bytes);
     int* xend = reinterpret_cast<int*>(nms + map_bytes + 2 * cnt_bytes + bm_bytes);
@@ -849,7 +876,7 @@ int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int qui
             qr.level[qr.n] = L; qr.row_base[qr.n + 1] = qr.row_base[qr.n] + lt.h[L]; ++qr.n;
         }
         if (qr.n > 0) {
-            CLB_CUDA(launch_ex(fast_xend_kernel, dim3((qr.row_base[qr.n] + 7) / 8), dim3(256), 0, s, pdl, lt, rm, qr, thresh, xend));
+            CLB_CUDA(launch_ex(fast_xend_kernel, dim3((qr.row_base[qr.n] + 3) / 4), dim3(128), 0, s, pdl, lt, rm, qr, thresh, xend));
             CLB_LAUNCHED();
         }
     }
@@ -902,14 +929,9 @@ int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int qui
 
 // offset / length (32-bit words) of the row counters + tile bitmap inside the scratch buffer: the resize kernel clears them
 void fast_clear_region(const LevelTable& lt, void* scratch, uint32_t** ptr, int* words) {
-    size_t rows = 0;
-    for (int i = 0; i < lt.n; ++i) rows += lt.h[i];
-    const size_t map_bytes = (rows * (size_t)lt.stride[0] + 255) & ~(size_t)255;
-    const size_t cnt_bytes = (rows * sizeof(int) + 255) & ~(size_t)255;
-    const size_t bm_words = ((size_t)((lt.w[0] + FT_TW - 1) / FT_TW) + 31) / 32;
-    const size_t bm_bytes = (rows * bm_words * 4 + 255) & ~(size_t)255;
-    *ptr = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + map_bytes);
-    *words = (int)((cnt_bytes + bm_bytes) / 4);
+    const FastLayout f = fast_layout(lt);
+    *ptr = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + f.map_bytes);
+    *words = (int)((f.cnt_bytes + f.bm_bytes) / 4);
 }
 
 }  // namespace clb
