@@ -315,6 +315,13 @@ class Matcher:
         _check(lib().clb_match_2nn_ratio(self._h, _ptr(Q), nQ, _ptr(T), nT, C.c_float(r), _ptr(m), _ptr(b), _ptr(s)))
         return (m, b, s) if want_dist else m
 
+    def match_filtered(self, A, B, filter=1, ratio=0.8):
+        """matching::Filter (matching_filters.hpp:118-213): 1 symmetric cross-check, 2 distance ratio, 3 both -> (k, 2) uint32"""
+        A, nA = self._rows(A); B, nB = self._rows(B)
+        out = np.zeros((max(nA, 1), 2), np.uint32); n = C.c_int(0)
+        _check(lib().clb_match_filtered(self._h, _ptr(A), nA, _ptr(B), nB, int(filter), C.c_float(ratio), _ptr(out), len(out), C.byref(n)))
+        return out[:n.value].copy()
+
     def set_map_data(self, M):
         """GPUMatcher::setMapData (GPUMatcher.hpp:110-117)."""
         M, nM = self._rows(M)

@@ -192,6 +192,10 @@ int run_views(clb_matcher* m, const clb::PairView* v, int nv, int threshold, flo
     long long units = 0, strips = 0;
     int max_nQ = 0;
     for (int p = 0; p < nv; ++p) {
+        // the sweep reads query rows and operand images as 128-bit words: a misaligned pointer is an argument error, not a fault
+        if (v[p].nQ > 0 && v[p].nT > 0 && ((reinterpret_cast<uintptr_t>(v[p].Q) | reinterpret_cast<uintptr_t>(v[p].Tx)) & 15)) {
+            snprintf(g_err, sizeof(g_err), "descriptor pointers must be 16-byte aligned"); return CLB_EINVAL;
+        }
         nQ[p] = v[p].nQ > 0 ? v[p].nQ : 0; nT[p] = v[p].nT;
         if (nQ[p] > max_nQ) max_nQ = nQ[p];
         if (nQ[p] <= 0 || nT[p] <= 0) continue;
@@ -385,6 +389,71 @@ int clb_match_pairs(clb_matcher* m, clb_fmap* f, const clb_pair* pairs, int npai
     if (second_d_out) CLB_CUDA(cudaMemcpyAsync(second_d_out, o + 2 * tot, (size_t)tot * 4, cudaMemcpyDeviceToHost, s));
     CLB_CUDA(cudaStreamSynchronize(s));
     return CLB_OK;
+}
+
+// ---- matching::Filter (matching_filters.hpp:118-213): symmetric (cross-check) and / or distance-ratio filtering of 2-NN lists ----
+}  // extern "C"
+namespace {
+__global__ void __launch_bounds__(256)
+filter_flags_kernel(const int32_t* __restrict__ m01, const int32_t* __restrict__ best01, const int32_t* __restrict__ second01,
+                    const int32_t* __restrict__ m10, int nA, int nB, float ratio, uint8_t* __restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nA) return;
+    const int j = m01[i];
+    // SymmetricMatches (:76-94): index == vec_reversematches[vec_matches[i * NN] * NN]
+    const bool sym = j >= 0 && j < nB && m10[j] == i;
+    // NNdistanceRatio (:39-60): *iter < fratio * *(iter + 1), on the float distances
+    const bool rat = (float)best01[i] < ratio * (float)second01[i];
+    flags[i] = (uint8_t)((sym ? 1 : 0) | (rat ? 2 : 0));
+}
+}  // namespace
+extern "C" {
+
+int clb_match_filtered(clb_matcher* m, const uint64_t* A, int nA, const uint64_t* B, int nB, int filter, float ratio,
+                       uint32_t* pairs_out, int cap, int* n_out) {
+    if (!m || !A || !B || !n_out || nA < 1 || nB < 1 || filter < 1 || filter > 3 || cap < 0 || (cap > 0 && !pairs_out)) {
+        snprintf(g_err, sizeof(g_err), "bad arguments (filter 1 = symmetric, 2 = distance ratio, 3 = both; both sets non-empty)"); return CLB_EINVAL;
+    }
+    if ((filter & 2) && (nA < 2 || nB < 2)) { snprintf(g_err, sizeof(g_err), "the distance-ratio filter needs two neighbours: at least two rows per set"); return CLB_EINVAL; }
+    CLB_CUDA(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const size_t tot = (size_t)nA + nB;
+    CLB_CUDA(m->q.reserve((size_t)nA * 64));
+    CLB_CUDA(m->t.reserve((size_t)nB * 64));
+    CLB_CUDA(m->qx.reserve(tc4_t_bytes(nA) + 16));
+    CLB_CUDA(m->tx.reserve(tc4_t_bytes(nB) + 16));
+    CLB_CUDA(m->pair_out.reserve(tot * 12 + (size_t)nA + 256));
+    CLB_CUDA(cudaMemcpyAsync(m->q.p, A, (size_t)nA * 64, cudaMemcpyHostToDevice, s));
+    CLB_CUDA(cudaMemcpyAsync(m->t.p, B, (size_t)nB * 64, cudaMemcpyHostToDevice, s));
+    int rc = launch_expand4(m->q.as<uint64_t>(), nA, m->qx.p, s);
+    if (rc) return rc;
+    rc = launch_expand4(m->t.as<uint64_t>(), nB, m->tx.p, s);
+    if (rc) return rc;
+    // both directions in ONE sweep launch: (A rows -> B image) and (B rows -> A image); threshold -1 keeps every best index
+    PairView v[2];
+    v[0].Q = m->q.as<uint64_t>(); v[0].nQ = nA; v[0].Tx = m->tx.as<uint8_t>(); v[0].nT = nB;
+    v[1].Q = m->t.as<uint64_t>(); v[1].nQ = nB; v[1].Tx = m->qx.as<uint8_t>(); v[1].nT = nA;
+    int32_t* o = m->pair_out.as<int32_t>();
+    rc = run_views(m, v, 2, -1, 0.f, o, o + tot, o + 2 * tot, nullptr, 0, s);
+    if (rc) return rc;
+    uint8_t* d_flags = reinterpret_cast<uint8_t*>(o + 3 * tot);
+    filter_flags_kernel<<<(nA + 255) / 256, 256, 0, s>>>(o, o + tot, o + 2 * tot, o + nA, nA, nB, ratio, d_flags);
+    CLB_LAUNCHED();
+    std::vector<int32_t> m01((size_t)nA);
+    std::vector<uint8_t> fl((size_t)nA);
+    CLB_CUDA(cudaMemcpyAsync(m01.data(), o, (size_t)nA * 4, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaMemcpyAsync(fl.data(), d_flags, (size_t)nA, cudaMemcpyDeviceToHost, s));
+    CLB_CUDA(cudaStreamSynchronize(s));
+    // index lists as Filter() builds them; its output loops stop one short of each list's end (`i < size() - 1`,
+    // matching_filters.hpp:175,184,199): the LAST surviving index is dropped, and so it is here
+    const uint8_t need = (uint8_t)filter;
+    std::vector<int> idx;
+    for (int i = 0; i < nA; ++i) if ((fl[(size_t)i] & need) == need) idx.push_back(i);
+    const int n = idx.empty() ? 0 : (int)idx.size() - 1;
+    *n_out = n;
+    if (n > cap) return CLB_ECAPACITY;
+    for (int k = 0; k < n; ++k) { pairs_out[2 * k] = (uint32_t)idx[(size_t)k]; pairs_out[2 * k + 1] = (uint32_t)m01[(size_t)idx[(size_t)k]]; }
+    return CLB_OK;      // ascending in i_ and unique by construction = the state after Filter()'s sort + unique
 }
 
 // ---- map database: setupMapDatabase (colocData.hpp:89-121) + setMapData (GPUMatcher.hpp:110-117) on the device ----

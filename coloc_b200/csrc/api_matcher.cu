@@ -37,7 +37,10 @@ static int match_dispatch(clb_matcher* m, const uint64_t* dQ, int nQ, const uint
 static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, bool map, cudaStream_t s,
                       const void** Qx, const void** Tx) {
     *Qx = nullptr; *Tx = nullptr;
-    if (!tc_wanted(nQ, nT)) return CLB_OK;
+    if (!tc_wanted(nQ, nT)) {
+        if (map && m->ev_map_set) CLB_CUDA(cudaStreamWaitEvent(s, m->ev_map, 0));
+        return CLB_OK;
+    }
     const size_t qb = tc_q_bytes(nQ), tb = tc_t_bytes(nT);
     int rc = CLB_OK;
     if (tc_needs_qx()) {
@@ -46,6 +49,7 @@ static int prepare_tc(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t
         if (rc) return rc;
         *Qx = m->qx.p;
     }
+    if (map && m->ev_map_set) CLB_CUDA(cudaStreamWaitEvent(s, m->ev_map, 0));      // the map may have been set on another stream
     if (map) {
         if (!m->mapx_valid || m->mapx_ver != tc_version()) {
             CLB_CUDA(m->mapx.reserve(tb));
@@ -171,7 +175,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     clb_matcher* m = new (std::nothrow) clb_matcher();
     if (!m) return CLB_ENOMEM;
     m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->mapx_ver = 0; m->stream = nullptr;
-    m->jobs_host = nullptr; m->jobs_host_cap = 0; m->jobs_ev_set = false; m->stream_ready = false; m->copy_stream = nullptr;
+    m->jobs_host = nullptr; m->jobs_host_cap = 0; m->jobs_ev_set = false; m->stream_ready = false; m->copy_stream = nullptr; m->ev_map_set = false;
     m->pending.set = false;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
@@ -190,6 +194,7 @@ void clb_matcher_destroy(clb_matcher* m) {
     m->jobs.release(); m->pair_part.release(); m->pair_out.release();
     if (m->jobs_host) cudaFreeHost(m->jobs_host);
     if (m->jobs_ev_set) cudaEventDestroy(m->jobs_ev);
+    if (m->ev_map_set) cudaEventDestroy(m->ev_map);
     if (m->stream_ready) {
         for (int b = 0; b < 2; ++b) { cudaEventDestroy(m->ev_copied[b]); cudaEventDestroy(m->ev_rawfree[b]); }
         cudaEventDestroy(m->ev_entry);
@@ -295,6 +300,8 @@ int clb_set_map_dev(clb_matcher* m, const uint64_t* dM, int nM, void* stream) {
     cudaStream_t s = stream ? (cudaStream_t)stream : m->stream;
     CLB_CUDA(m->map.reserve((size_t)(nM > 0 ? nM : 1) * 64));
     if (nM > 0) CLB_CUDA(cudaMemcpyAsync(m->map.p, dM, (size_t)nM * 64, cudaMemcpyDeviceToDevice, s));
+    if (!m->ev_map_set) { CLB_CUDA(cudaEventCreateWithFlags(&m->ev_map, cudaEventDisableTiming)); m->ev_map_set = true; }
+    CLB_CUDA(cudaEventRecord(m->ev_map, s));      // later map sweeps, on whatever stream, are ordered behind this copy
     m->n_map = nM;
     m->mapx_valid = false;
     return CLB_OK;

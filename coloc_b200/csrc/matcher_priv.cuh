@@ -9,6 +9,8 @@ struct clb_matcher {
     clb::DevBuf q, t, map, scratch, out;   // out: match | best | second (3 x nQ int32)
     clb::DevBuf qx, tx, mapx;              // +-1 expansions for the tensor-core path (match_tc.cu)
     int n_map;
+    cudaEvent_t ev_map;                    // recorded behind the copy of clb_set_map_dev / clb_set_map_from_fmap: map sweeps on any stream wait on it
+    bool ev_map_set;
     bool mapx_valid;
     int mapx_ver;                          // kernel version the cached map expansion was made for
     // pair lists (api_fmap.cu): job tables staged in pinned memory, per-chunk partials, host-call output

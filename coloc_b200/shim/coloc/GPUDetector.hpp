@@ -6,6 +6,7 @@
 // `return EXIT_SUCCESS` (=0) on success (GPUDetector.hpp:183, tested `== EXIT_SUCCESS` at coloc.hpp:241);
 // errors print and exit like gpuErrchk (GPUMatcher.hpp:33-41).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -13,8 +14,24 @@
 #include <string>
 #include <vector>
 #include "coloc_b200.h"
-#ifdef CLB_SHIM_STANDALONE
+// Three builds of the same shim:
+//   (default)             inside the reference tree: real coloc/colocData.hpp (openMVG + SfM types) and cv::imread
+//   CLB_SHIM_OPENMVG      the real openMVG boundary types (regions_factory.hpp, indMatch.hpp, types.hpp) without the SfM / ceres /
+//                         OpenCV part of the tree: what this repo's compile test uses when /root/reference is present
+//   CLB_SHIM_STANDALONE   no openMVG at all: the 60-line stand-ins of openmvg_min.hpp (tests on the GPU box, demos)
+#if defined(CLB_SHIM_STANDALONE)
 #include "openmvg_min.hpp"
+#elif defined(CLB_SHIM_OPENMVG)
+#include <map>
+#include <memory>
+#include "openMVG/types.hpp"
+#include "openMVG/features/regions_factory.hpp"
+#include "openMVG/matching/indMatch.hpp"
+namespace coloc {      // include/coloc/colocData.hpp:19-42, the part of it the detector / matcher boundary touches
+using FeatureMap = std::map<openMVG::IndexT, std::unique_ptr<openMVG::features::AKAZE_Binary_Regions>>;
+struct DetectorOptions { float scale_factor; uint8_t scale_levels; unsigned int width, height, maxkp; uint8_t thresh; };
+struct MatcherOptions { float distRatio; int thresh; unsigned int maxkp; };
+}  // namespace coloc
 #else
 #include <opencv2/imgcodecs.hpp>
 #include "coloc/colocData.hpp"
@@ -63,7 +80,10 @@ public:
         cap = o.maxkp;
     }
     ~GPUDetector() {}                         // the reference leaks on purpose; freeGPUMemory() is explicit
-    void freeGPUMemory() { clb_detector_destroy(det); det = nullptr; }   // GPUDetector.hpp:144-155
+    void freeGPUMemory() {                    // GPUDetector.hpp:144-155
+        clb_detector_destroy(det); det = nullptr;
+        clb_host_free(h_kps); clb_host_free(h_desc); h_kps = nullptr; h_desc = nullptr;
+    }
 
     // GPUDetector.hpp:158-184
     T detectFeaturesFile(uint8_t idx, coloc::FeatureMap& regions, std::string& imageName) {
@@ -93,16 +113,26 @@ public:
 
 private:
     // GPUDetector.hpp:216-291: H2D, pyramid, FAST+NMS+angle, LATCH, D2H -- one ABI call
+    // The results land in page-locked scratch that lives as long as the detector (the describe kernel writes the descriptors
+    // straight into it, clb_detect_describe); only the n entries of this frame are copied into the public vectors -- no
+    // value-initialisation of `cap` entries (43 MB at 4K) per frame.
     void detectAndDescribe(const uint8_t* image, const uint32_t width, const uint32_t height, const uint8_t) {
-        kps.resize(cap); desc.resize(8 * (size_t)cap);
+        if (!h_kps) {
+            void* p = nullptr;
+            clbCheck(clb_host_alloc((size_t)cap * sizeof(clb_keypoint), &p), "clb_host_alloc"); h_kps = static_cast<clb_keypoint*>(p);
+            clbCheck(clb_host_alloc((size_t)cap * 64, &p), "clb_host_alloc"); h_desc = static_cast<uint64_t*>(p);
+        }
         int n = 0;
-        clbCheck(clb_detect_describe(det, image, (int)width, (int)height, (int)width,
-                                     reinterpret_cast<clb_keypoint*>(kps.data()), desc.data(), cap, &n), "clb_detect_describe");
-        kps.resize(n); desc.resize(8 * (size_t)n);
+        clbCheck(clb_detect_describe(det, image, (int)width, (int)height, (int)width, h_kps, h_desc, cap, &n), "clb_detect_describe");
+        kps.resize((size_t)n); desc.resize(8 * (size_t)n);
+        if (n > 0) {
+            std::memcpy(static_cast<void*>(kps.data()), h_kps, (size_t)n * sizeof(clb_keypoint));
+            std::memcpy(desc.data(), h_desc, (size_t)n * 64);
+        }
     }
 
     static const uint8_t* loadGray(const std::string& name, int& w, int& h, std::vector<uint8_t>& own) {
-#ifdef CLB_SHIM_STANDALONE
+#if defined(CLB_SHIM_STANDALONE) || defined(CLB_SHIM_OPENMVG)
         // binary PGM (P5, maxval 255) only
         FILE* f = std::fopen(name.c_str(), "rb");
         if (!f) return nullptr;
@@ -124,6 +154,8 @@ private:
     }
 
     clb_detector* det = nullptr;
+    clb_keypoint* h_kps = nullptr;   // page-locked result scratch, cap entries
+    uint64_t* h_desc = nullptr;
     int cap = 0;
     const uint8_t thresh;
 };

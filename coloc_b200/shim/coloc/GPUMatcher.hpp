@@ -14,7 +14,7 @@
 
 namespace coloc {
 
-#ifdef CLB_SHIM_STANDALONE
+#if defined(CLB_SHIM_STANDALONE) || defined(CLB_SHIM_OPENMVG)
 // what matchSceneWithMap needs from colocData (include/coloc/colocData.hpp:45-122)
 struct colocData { FeatureMap regions; };
 using openMVG::Pair;
@@ -28,20 +28,35 @@ class GPUMatcher {
 public:
     unsigned int maxkpNum;
 
+    // COLOC_B200_DEVICES=0,1,2,... in the environment shards the map database over those GPUs (clb_sharded_*)
+    // without a change to the host code: setMapData cuts the rows over the devices, matchSceneWithMap / matchFeaturesWithMap
+    // sweep every shard and merge.  useDevices() does the same programmatically.  Pair matching stays on the first device.
     GPUMatcher(MatcherOptions opts) : maxkpNum(opts.maxkp), matchThreshold((uint8_t)opts.thresh) {
-        clb_matcher_opts o; o.distRatio = opts.distRatio; o.thresh = opts.thresh; o.maxkp = (int32_t)opts.maxkp;
+        o.distRatio = opts.distRatio; o.thresh = opts.thresh; o.maxkp = (int32_t)opts.maxkp;
         clbCheck(clb_matcher_create(&o, 0, &m), "clb_matcher_create");
+        if (const char* env = std::getenv("COLOC_B200_DEVICES")) {
+            std::vector<int> devs;
+            for (const char* p = env; *p;) { char* e = nullptr; const long v = std::strtol(p, &e, 10); if (e == p) break; devs.push_back((int)v); p = (*e == ',') ? e + 1 : e; }
+            if (devs.size() > 1) useDevices(devs);
+        }
     }
     ~GPUMatcher() { freeGPUMemory(); }
     void freeGPUMemory() {                                                          // :102-108
+        if (sharded) clb_sharded_destroy(sharded);
+        sharded = nullptr;
         if (fmap) clb_fmap_destroy(fmap);
         fmap = nullptr;
         if (m) clb_matcher_destroy(m);
         m = nullptr;
     }
+    void useDevices(const std::vector<int>& devices) {
+        if (sharded) { clb_sharded_destroy(sharded); sharded = nullptr; }
+        if (devices.size() > 1) clbCheck(clb_sharded_create(&o, devices.data(), (int)devices.size(), &sharded), "clb_sharded_create");
+    }
 
     void setMapData(int kpNum, void* desc) {                                        // :110-117
-        clbCheck(clb_set_map(m, static_cast<const uint64_t*>(desc), kpNum), "clb_set_map");
+        if (sharded) clbCheck(clb_sharded_set_map(sharded, static_cast<const uint64_t*>(desc), kpNum), "clb_sharded_set_map");
+        else         clbCheck(clb_set_map(m, static_cast<const uint64_t*>(desc), kpNum), "clb_set_map");
         kpMap = kpNum;
     }
     void setTrainingImage(int kpNum, std::vector<uint64_t> const& desc) {           // :120-127
@@ -115,6 +130,21 @@ public:
         return EXIT_SUCCESS;
     }
 
+    // matching::Filter over 2-NN lists in both directions (matching_filters.hpp:118-213): filter 1 = symmetric cross-check,
+    // 2 = distance ratio, 3 = both.  IndMatch(i_ = idx in pair.first, j_ = idx in pair.second).
+    T computeMatchesPairFiltered(const Pair& pairIdx, FeatureMap& regions, IndMatches& putativeMatches, int filter = 1, float distRatio = 0.8f) {
+        const auto& rI = regions.at(pairIdx.first);
+        const auto& rJ = regions.at(pairIdx.second);
+        const int nI = (int)rI->RegionCount(), nJ = (int)rJ->RegionCount();
+        std::vector<uint32_t> out((size_t)2 * (nI > 0 ? nI : 1));
+        int n = 0;
+        clbCheck(clb_match_filtered(m, static_cast<const uint64_t*>(rI->DescriptorRawData()), nI, static_cast<const uint64_t*>(rJ->DescriptorRawData()), nJ,
+                                    filter, distRatio, out.data(), nI > 0 ? nI : 1, &n), "clb_match_filtered");
+        putativeMatches.clear();
+        for (int k = 0; k < n; ++k) putativeMatches.emplace_back(out[2 * k], out[2 * k + 1]);
+        return EXIT_SUCCESS;
+    }
+
     void matchSceneWithMap(int& droneId, colocData& data, IndMatches& mapMatches) {                                     // :174-178
         setQueryImage((int)data.regions[droneId]->RegionCount(), const_cast<void*>(data.regions[droneId]->DescriptorRawData()));
         mapMatches = matchFeaturesWithMap();
@@ -145,7 +175,8 @@ public:
 
     IndMatches matchFeaturesWithMap() {                                             // :252-271
         h_matches.resize(kpQuery);
-        clbCheck(clb_match_map(m, query.data(), (int)kpQuery, matchThreshold, h_matches.data(), nullptr, nullptr), "clb_match_map");
+        if (sharded) clbCheck(clb_sharded_match_map(sharded, query.data(), (int)kpQuery, matchThreshold, h_matches.data(), nullptr, nullptr), "clb_sharded_match_map");
+        else         clbCheck(clb_match_map(m, query.data(), (int)kpQuery, matchThreshold, h_matches.data(), nullptr, nullptr), "clb_match_map");
         IndMatches matches;
         for (size_t i = 0; i < kpQuery; ++i)
             if (h_matches[i] != -1) matches.emplace_back(h_matches[i], (uint32_t)i);   // i_ = MAP idx, j_ = FRAME idx
@@ -153,7 +184,9 @@ public:
     }
 
 private:
+    clb_matcher_opts o;
     clb_matcher* m = nullptr;
+    clb_sharded* sharded = nullptr;   // map database cut over several GPUs (COLOC_B200_DEVICES / useDevices)
     clb_fmap* fmap = nullptr;      // device-side copy of the FeatureMap used by computeMatches(FeatureMap&, ...)
     unsigned int kpTrain = 0, kpQuery = 0, kpMap = 0;
     uint8_t matchThreshold;

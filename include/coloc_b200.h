@@ -11,6 +11,11 @@
  * CUDAK2NN.cu:80).  `_dev` entry points take DEVICE pointers plus a cudaStream_t (passed as
  * void*) and only enqueue work; a NULL stream means the object's own (non-blocking) stream, pass
  * cudaStreamLegacy / cudaStreamPerThread explicitly to use a default stream.
+ *
+ * Concurrency contract: an object (detector, matcher, fmap, sharded, stream) owns ONE set of device scratch buffers, so one
+ * call per object may be in flight at a time -- consecutive `_dev` calls on the SAME stream are ordered by it; before using
+ * an object from a different stream, synchronise the previous one.  (The map copy of clb_set_map_dev is the exception: later
+ * map sweeps on any stream wait for it by event.)  Objects are not thread-safe; different objects are independent.
  */
 #ifndef COLOC_B200_H
 #define COLOC_B200_H
@@ -304,6 +309,15 @@ int  clb_dedup_matches(const int32_t* match, int nQ, const float* featsI, int st
 int  clb_distance_ratio_match(clb_matcher* m, const uint64_t* descI, const float* featsI, int nI,
                               const uint64_t* descJ, const float* featsJ, int nJ, float ratio,
                               uint32_t* pairs_out, int cap, int* n_out);
+
+/* matching::Filter (matching_filters.hpp:118-213) over brute-force Hamming 2-NN lists in BOTH directions:
+ * filter 1 = MATCHFILTER_SYMMETRIC (keep i iff the nearest row of B to A[i] has A[i] as ITS nearest row, SymmetricMatches :76-94),
+ * 2 = MATCHFILTER_NNDISTANCERATIO (:39-60), 3 = both.  One GPU sweep launch covers both directions.  pairs_out = (i_, j_) =
+ * (row of A, row of B), ascending, as Filter() leaves them -- including its loops that stop one short of the list's end (the last
+ * surviving index is dropped).  Nearest rows resolve distance ties to the lowest index (CUDAK2NN.cu:67-72); openMVG's
+ * partial_sort leaves ties unspecified.  HOST pointers.  CLB_ECAPACITY with *n_out = needed pairs. */
+int  clb_match_filtered(clb_matcher* m, const uint64_t* A, int nA, const uint64_t* B, int nB, int filter, float ratio,
+                        uint32_t* pairs_out, int cap, int* n_out);
 
 /* ---------------------------------------------------------------- geometric pre-filter --- */
 /* SURVEY 8(f)-4.  The Errors() pass of the AC-RANSAC kernel adaptors (robust_estimator_ACRansacKernelAdaptator.hpp:93-99,

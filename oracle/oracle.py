@@ -298,6 +298,29 @@ def ref_distance_ratio_match(desc_i, feats_i, desc_j, feats_j, ratio=0.8):
     return out[:n]
 
 
+def ref_filter_matches(A, B, filter=1, ratio=0.8):
+    """the reference's matching::Filter over its own brute-force 2-NN in both directions (compiled openMVG); (k, 2) uint32"""
+    A = np.ascontiguousarray(A, np.uint64).reshape(-1, 8); B = np.ascontiguousarray(B, np.uint64).reshape(-1, 8)
+    out = np.zeros((max(1, len(A)), 2), np.uint32)
+    n = ref_cpu().ref_filter_matches(A.ctypes.data_as(_u8p), len(A), B.ctypes.data_as(_u8p), len(B), int(filter), C.c_float(ratio),
+                                     out.ctypes.data_as(C.c_void_p), len(out))
+    return None if n < 0 else out[:n]
+
+
+def filter_matches(A, B, filter=1, ratio=0.8):
+    """restatement of matching::Filter on the oracle's 2-NN (first row wins ties), incl. the dropped last index"""
+    m01, b01, s01 = match_2nn(A, B, -1)
+    m10, _, _ = match_2nn(B, A, -1)
+    idx = []
+    for i in range(len(m01)):
+        sym = m01[i] >= 0 and m10[m01[i]] == i
+        rat = np.float32(b01[i]) < np.float32(ratio) * np.float32(s01[i])
+        if ((filter & 1) == 0 or sym) and ((filter & 2) == 0 or rat):
+            idx.append(i)
+    idx = idx[:-1]
+    return np.array([(i, m01[i]) for i in idx], np.uint32).reshape(-1, 2)
+
+
 _f64p = C.POINTER(C.c_double)
 
 

@@ -78,6 +78,28 @@ int ref_bruteforce_2nn(const uint8_t* T, int nT, const uint8_t* Q, int nQ, float
     return 0;
 }
 
+// matching::Filter (matching_filters.hpp:118-213) over openMVG's own brute-force 2-NN lists in both directions.
+// filter: 1 symmetric, 2 distance ratio, 3 both.  pairs: (i_, j_) per kept match; returns the count (or -1).
+int ref_filter_matches(const uint8_t* A, int nA, const uint8_t* B, int nB, int filter, float ratio, uint32_t* pairs, int cap) {
+    using namespace openMVG::matching;
+    using Matcher = ArrayMatcherBruteForce<unsigned char, Hamming<unsigned char>>;
+    Matcher mB, mA;
+    if (!mB.Build(B, nB, 64) || !mA.Build(A, nA, 64)) return -1;
+    IndMatches i01, i10;
+    std::vector<Matcher::DistanceType> d01, d10;
+    const int NN = 2;
+    if (!mB.SearchNeighbours(A, nA, &i01, &d01, NN) || !mA.SearchNeighbours(B, nB, &i10, &d10, NN)) return -1;
+    std::vector<int> v01(i01.size()), v10(i10.size());
+    std::vector<float> f01(d01.begin(), d01.end()), f10(d10.begin(), d10.end());
+    for (size_t k = 0; k < i01.size(); ++k) v01[k] = (int)i01[k].j_;
+    for (size_t k = 0; k < i10.size(); ++k) v10[k] = (int)i10[k].j_;
+    std::vector<IndMatch> out;
+    Filter(NN, v01, f01, v10, f10, out, (eMatchFilter)filter, ratio);
+    int n = 0;
+    for (const IndMatch& m : out) { if (n < cap) { pairs[2 * n] = m.i_; pairs[2 * n + 1] = m.j_; } ++n; }
+    return n;
+}
+
 static void fill_regions(openMVG::features::AKAZE_Binary_Regions& r, const float* feats, const uint8_t* desc, int n) {
     r.Features().resize(n); r.Descriptors().resize(n);
     for (int i = 0; i < n; ++i) {

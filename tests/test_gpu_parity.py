@@ -813,3 +813,23 @@ def test_match_balanced_jobs_vs_oracle(clb, oracle, nq, nt):
         m.close()
     finally:
         clb.set_param("match_tc", -1); clb.set_param("match_balance", -1)
+
+
+@pytest.mark.parametrize("flt", [1, 2, 3])
+def test_match_filtered_equals_reference(clb, oracle, flt):
+    """clb_match_filtered (symmetric cross-check / distance ratio / both over 2-NN lists in both directions, one GPU
+    sweep) == matching::Filter: the restatement, and the reference's compiled code when oracle/_ref is there"""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from _helpers import filter_problem
+    A, B = filter_problem()
+    m = clb.Matcher(maxkp=1024)
+    got = m.match_filtered(A, B, flt, 0.8)
+    assert np.array_equal(got, oracle.filter_matches(A, B, flt, 0.8))
+    if oracle.ref_cpu() is not None:
+        assert np.array_equal(got, oracle.ref_filter_matches(A, B, flt, 0.8))
+    got = m.match_filtered(B, A, flt, 0.8)                                # the other way round, and a second call on the same matcher
+    assert np.array_equal(got, oracle.filter_matches(B, A, flt, 0.8))
+    with pytest.raises(clb.ClbError):
+        m.match_filtered(A[:1], B, 2, 0.8)
+    m.close()

@@ -236,3 +236,21 @@ def test_golden_match(oracle):
     g = _gold("match_small.npz")
     m, b, s = oracle.match_2nn(g["Q"], g["T"], int(g["threshold"]))
     assert np.array_equal(m, g["match"]) and np.array_equal(b, g["best"]) and np.array_equal(s, g["second"])
+
+
+@pytest.mark.parametrize("flt", [1, 2, 3])
+def test_filter_matches_equals_openmvg(ref_cpu, flt):
+    """matching::Filter (matching_filters.hpp:118-213: SymmetricMatches / NNdistanceRatio / both, with its `size() - 1` output
+    loops) compiled from the submodule, against the restatement the GPU test uses"""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from _helpers import filter_problem
+    O = ref_cpu
+    A, B = filter_problem()
+    ref = O.ref_filter_matches(A, B, flt, 0.8)
+    mine = O.filter_matches(A, B, flt, 0.8)
+    assert ref is not None and len(ref) > 100 and np.array_equal(ref, mine)
+    if flt == 1:
+        assert len(ref) < len(O.filter_matches(A, B, 2, 0.8)) + 400        # sanity: lists differ in general
+    sym = set(map(tuple, O.filter_matches(A, B, 1, 0.8))); rat = set(map(tuple, O.filter_matches(A, B, 2, 0.8)))
+    assert sym != rat                                                      # the cross-check and the ratio test reject different rows

@@ -24,6 +24,25 @@ def _build(out):
                            SRC, "-L", libdir, "-lcoloc_b200", f"-Wl,-rpath,{libdir}", "-o", out])
 
 
+def test_shim_compiles_against_real_openmvg_headers(tmp_path):
+    """the same shim + driver against the reference's OWN openMVG boundary types (regions_factory.hpp, indMatch.hpp, types.hpp
+    from the submodule, Eigen and cereal vendored there) instead of the stand-ins -- only where /root/reference exists"""
+    ref = "/root/reference/lib/openMVG/src"
+    if not os.path.isdir(ref):
+        pytest.skip("no /root/reference on this box")
+    import coloc_b200
+    if not os.path.exists(coloc_b200.lib_path()):
+        coloc_b200.build()
+    libdir = os.path.join(ROOT, "coloc_b200")
+    exe = str(tmp_path / "shim_driver_omvg")
+    subprocess.check_call(["/usr/bin/g++", "-std=c++14", "-Wall", "-Wno-deprecated-declarations", "-Wno-unused-local-typedefs", "-DCLB_SHIM_OPENMVG",
+                           "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "coloc_b200", "shim"),
+                           "-I", ref, "-I", os.path.join(ref, "third_party", "eigen"), "-I", os.path.join(ref, "dependencies", "cereal", "include"),
+                           SRC, os.path.join(ref, "openMVG", "features", "feature.cpp"),      # SIOPointFeature's out-of-line members
+                           "-L", libdir, "-lcoloc_b200", f"-Wl,-rpath,{libdir}", "-o", exe])
+    assert subprocess.call([exe]) == 2
+
+
 def test_shim_compiles_and_links(tmp_path):
     exe = str(tmp_path / "shim_driver")
     _build(exe)
