@@ -477,12 +477,12 @@ def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
     def step_list():                                          # the whole pair list: one sweep launch + one merge launch
         m.match_pairs_dev(fm, jobs, 40, mine, stream=st)
 
-    def timed(fn):
+    def timed(fn, gather=True):
         def step():
             fn()
-            if world > 1:
+            if world > 1 and gather:
                 dist.all_gather_into_tensor(allm.view(-1), mine)
-            else:
+            elif world == 1:
                 allm[0].copy_(mine)
         for _ in range(3):
             step()
@@ -503,6 +503,7 @@ def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
     ref_rows = allm.clone()
     ms = timed(step_list)
     same = bool(torch.equal(ref_rows, allm))
+    ms_nogather = timed(step_list, gather=False)            # the same step without the exchange: what the all-gather costs
     cmp_step = float(sum(counts[q] * counts[t] for q, t in pairs))
     got = allm.cpu().numpy()
     matched = int(sum((got[r][:shard.shard_range(total_rows, r, world)[1] - shard.shard_range(total_rows, r, world)[0]] >= 0).sum()
@@ -510,6 +511,7 @@ def c3_extra(clb, torch, dist, synth, shard, rank, world, dev, steps=5):
     m.close(); fm.close()
     return {"frames": 4, "pairs": 12, "keypoints": counts, "query_rows": total_rows, "comparisons_per_step": cmp_step,
             "ms_per_step": ms, "comparisons_per_s": cmp_step / (ms * 1e-3), "matched_rows": matched,
+            "ms_per_step_without_allgather": ms_nogather, "allgather_share": (ms - ms_nogather) / ms if ms > 0 else None,
             "api": "clb_match_pairs_dev over a device FeatureMap (one sweep + one merge launch per step)",
             "per_pair_calls": {"ms_per_step": ms_calls, "comparisons_per_s": cmp_step / (ms_calls * 1e-3), "same_matches": same},
             "parallelism": f"query rows x{world}, all-gather of int32 match lists"}
@@ -575,8 +577,9 @@ def run_ours(args, rank, world, local_rank):
     for i in range(args.steps):
         flush.fill_(i & 0xFF)                          # L2 flush between steps, outside the event pair
         ev[i][0].record(); step_resident(); ev[i][1].record()
-        torch.cuda.synchronize()
-        kernel_ms.append(clb.last_kernel_ms("match"))
+        if i < 2 or i == args.steps - 1:               # the library keeps the last launch's event pair: sample a few steps, do not
+            torch.cuda.synchronize()                   # drain the stream after every one (the host then enqueues step i+1 while
+            kernel_ms.append(clb.last_kernel_ms("match"))   # step i runs, as a caller that pipelines its frames would)
     barrier()
     launches = clb.launch_count() - launches0
     clb.set_timing(False)
@@ -627,8 +630,11 @@ def run_ours(args, rank, world, local_rank):
     del dT, flush
     c3 = c3_extra(clb, torch, dist, synth, shard, rank, world, dev)      # collective: every rank takes part
     streams = {}
-    for key, a in (("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
-                   ("c5_stream_detect_describe_match", (3840, 2160, 256, True))):
+    cfgs = [("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
+            ("c5_stream_detect_describe_match", (3840, 2160, 256, True))]
+    if world > 1:      # 256 frames over 8 ranks are 32 frames per pipeline: the same streams `world` times longer show the rate without fill / drain
+        cfgs += [("c2_stream_detect_describe_match_long", (1280, 720, 256 * world, True)), ("c5_stream_detect_describe_match_long", (3840, 2160, 256 * world, True))]
+    for key, a in cfgs:
         ok = 1
         try:
             streams[key] = stream_extra(clb, torch, dist, synth, *a, rank=rank, world=world, dev=dev)

@@ -90,7 +90,14 @@ def launch_count():
 
 
 def set_timing(on):
-    lib().clb_set_timing(int(bool(on)))
+    lib().clb_set_timing(int(on))
+
+
+def timeline():
+    """[(name, ms)] of the marks recorded since the last call (set_timing(2))"""
+    buf = C.create_string_buffer(1 << 16)
+    _check(lib().clb_timeline(buf, len(buf)))
+    return [(a.rsplit(":", 1)[0], float(a.rsplit(":", 1)[1])) for a in buf.value.decode().split()]
 
 
 def last_kernel_ms(which):

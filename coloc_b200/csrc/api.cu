@@ -6,6 +6,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <vector>
 #include <new>
 
 namespace clb {
@@ -24,6 +25,17 @@ static std::map<std::string, KernelTimer> g_timers;
 KernelTimer& timer(const char* which) {
     std::lock_guard<std::mutex> lk(g_timer_mu);
     return g_timers[which];
+}
+struct TlMark { std::string name; cudaEvent_t ev; };
+static std::vector<TlMark> g_tl;
+void tl_mark(const char* name, cudaStream_t s) {
+    if (g_timing.load() != 2) return;
+    std::lock_guard<std::mutex> lk(g_timer_mu);
+    if (g_tl.size() >= 512) return;
+    TlMark m; m.name = name;
+    if (cudaEventCreate(&m.ev) != cudaSuccess) return;
+    cudaEventRecord(m.ev, s);
+    g_tl.push_back(m);
 }
 }  // namespace clb
 
@@ -167,6 +179,25 @@ int clb_version(void) { return 100; }
 int clb_device_count(int* n_out) { if (!n_out) return CLB_EINVAL; CLB_CUDA(cudaGetDeviceCount(n_out)); return CLB_OK; }
 int64_t clb_launch_count(void) { return g_launches.load(); }
 int clb_set_timing(int on) { g_timing = on; return CLB_OK; }
+// "name:ms name:ms ..." of the marks recorded since the last call (timing level 2), offsets from the first mark; clears them
+int clb_timeline(char* buf, int cap) {
+    if (!buf || cap < 2) return CLB_EINVAL;
+    std::lock_guard<std::mutex> lk(g_timer_mu);
+    buf[0] = 0;
+    int off = 0;
+    for (size_t i = 0; i < g_tl.size(); ++i) {
+        cudaEventSynchronize(g_tl[i].ev);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, g_tl[0].ev, g_tl[i].ev);
+        const int n = snprintf(buf + off, (size_t)(cap - off), "%s%s:%.4f", i ? " " : "", g_tl[i].name.c_str(), ms);
+        if (n < 0 || n >= cap - off) break;
+        off += n;
+    }
+    for (auto& m : g_tl) cudaEventDestroy(m.ev);
+    g_tl.clear();
+    cudaGetLastError();
+    return CLB_OK;
+}
 float clb_last_kernel_ms(const char* which) { return which ? timer(which).ms() : 0.f; }
 // Planning knobs are process-wide atomics (set them before the calls they should affect); kernel-variant and timing knobs
 // exist in the lab build only and answer CLB_EUNSUPPORTED here otherwise, so a stray call cannot change what the product runs.

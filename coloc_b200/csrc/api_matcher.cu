@@ -105,8 +105,10 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
     const int slice_knob = g_match_slice_rows;
     int first = slice_knob < 1024 ? 1024 : slice_knob;
     // a shard of a sharded map (250 k rows per GPU at 8 GPUs) is smaller than the default first slice and its whole copy would sit
-    // in front of the sweep: first slice <= a quarter of the rows, but not below 64 Ki rows (match_slice_rows >= 2^30: never cut)
-    if (first > nT / 4 && slice_knob < (1 << 30)) first = nT / 4 > 65536 ? nT / 4 : (first < 65536 ? first : 65536);
+    // in front of the sweep: first slice <= a quarter of the rows; shards below 256 Ki rows start with 32 Ki rows -- with 8 ranks
+    // pulling from one host a rank sees ~21 GB/s, so every 16 Ki rows in front of the first sweep are 50 us of the step
+    // (profiles/r2_e2e_timeline.md) (match_slice_rows >= 2^30: never cut)
+    if (first > nT / 4 && slice_knob < (1 << 30)) first = nT / 4 > 65536 ? nT / 4 : (first < 32768 ? first : 32768);
     first = (first + 127) & ~127;
     int nsl = 0, rows_max = 0;
     for (long long start = 0, sz = first; start < nT; start += sz, sz = sz * 4 > STREAM_MAX_SLICE ? STREAM_MAX_SLICE : sz * 4) {
@@ -147,8 +149,10 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
         const int b = k & 1;
         const int rows = (int)(nT - start < sz ? nT - start : sz);
         if (k >= 2) CLB_CUDA(cudaStreamWaitEvent(m->copy_stream, m->ev_rawfree[b], 0));
+        tl_mark("slice_copy_begin", m->copy_stream);
         CLB_CUDA(cudaMemcpyAsync(m->sraw[b].p, T_host + (size_t)start * 8, (size_t)rows * 64, cudaMemcpyHostToDevice, m->copy_stream));
         CLB_CUDA(cudaEventRecord(m->ev_copied[b], m->copy_stream));
+        tl_mark("slice_copy_end", m->copy_stream);
         // "wait for the copy, expand the slice" is handed to the sweep's launch path, which enqueues it AFTER its job-table
         // upload: parked behind the wait, that small upload became eligible only once the next slice's copy already held the
         // copy engine, and the sweep then sat out the whole copy (event timeline: a 0.85 ms sweep took 1.29 ms next to a
@@ -160,6 +164,7 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
         if (rc) { m->pending.set = false; return rc; }
         if (m->pending.set) { rc = clb_consume_pending(m, s); if (rc) return rc; }      // a path that launched nothing
         CLB_CUDA(cudaEventRecord(m->ev_rawfree[b], s));
+        tl_mark("slice_swept", s);
         start += sz;
         sz = sz * 4 > STREAM_MAX_SLICE ? STREAM_MAX_SLICE : sz * 4;
     }

@@ -271,16 +271,21 @@ int clb_sharded_match_map_dev(clb_sharded* s, const uint64_t* dQ, int nQ, int th
     const int thr = threshold < 0 ? s->o.thresh : threshold;
     CLB_CUDA(x.part.reserve((size_t)nQ * sizeof(clb_partial)));
     int rc;
+    tl_mark("sweep_begin", st);
     if (x.host_rows) rc = clb_match_partial_hostdb(x.m, dQ, nQ, x.host_rows, (int)(x.hi - x.lo), x.lo, x.part.as<clb_partial>(), st);
     else             rc = clb_match_map_partial_dev(x.m, dQ, nQ, x.lo, x.part.as<clb_partial>(), st);
     if (rc) return rc;
     const clb_partial* parts = x.part.as<clb_partial>();
+    tl_mark("sweep_end", st);
     if (s->n > 1) {
         CLB_CUDA(s->gath.reserve((size_t)s->n * nQ * sizeof(clb_partial)));
         CLB_NCCL(g_nccl.AllGather(x.part.p, s->gath.p, (size_t)nQ * sizeof(clb_partial), 0 /* ncclChar */, s->comm, st));
         parts = s->gath.as<clb_partial>();
+        tl_mark("allgather_end", st);
     }
-    return clb_merge_partials_dev(x.m, parts, s->n, nQ, thr, d_match_out, d_best_out, d_second_out, st);
+    rc = clb_merge_partials_dev(x.m, parts, s->n, nQ, thr, d_match_out, d_best_out, d_second_out, st);
+    tl_mark("merge_end", st);
+    return rc;
 }
 
 // matchFeaturesWithMap (GPUMatcher.hpp:252-271) over all shards, HOST queries in, HOST results out, blocking.
@@ -308,11 +313,13 @@ int clb_sharded_match_map(clb_sharded* s, const uint64_t* Q, int nQ, int thresho
     if (s->rank_mode) {
         cudaStream_t st = x0.stream;
         CLB_CUDA(x0.q.reserve(qbytes));
+        tl_mark("call_begin", st);
         if (x0.host_rows) {
             // the first DB slice is as urgent as the queries: give the query upload its own stream so that both DMA queues start at once
             if (!s->up_stream) { CLB_CUDA(cudaStreamCreateWithFlags(&s->up_stream, cudaStreamNonBlocking)); CLB_CUDA(cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming)); }
             CLB_CUDA(cudaMemcpyAsync(x0.q.p, src, qbytes, cudaMemcpyHostToDevice, s->up_stream));
             CLB_CUDA(cudaEventRecord(s->ev_up, s->up_stream));
+            tl_mark("queries_uploaded", s->up_stream);
             CLB_CUDA(cudaStreamWaitEvent(st, s->ev_up, 0));
         } else {
             CLB_CUDA(cudaMemcpyAsync(x0.q.p, src, qbytes, cudaMemcpyHostToDevice, st));
@@ -344,6 +351,7 @@ int clb_sharded_match_map(clb_sharded* s, const uint64_t* Q, int nQ, int thresho
     CLB_CUDA(cudaMemcpyAsync(match_out, o, (size_t)nQ * 4, cudaMemcpyDeviceToHost, st));
     if (best_d_out) CLB_CUDA(cudaMemcpyAsync(best_d_out, o + nQ, (size_t)nQ * 4, cudaMemcpyDeviceToHost, st));
     if (second_d_out) CLB_CUDA(cudaMemcpyAsync(second_d_out, o + 2 * (size_t)nQ, (size_t)nQ * 4, cudaMemcpyDeviceToHost, st));
+    tl_mark("results_on_host", st);
     CLB_CUDA(cudaStreamSynchronize(st));
     return CLB_OK;
 }

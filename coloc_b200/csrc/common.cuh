@@ -58,6 +58,9 @@ struct KernelTimer {
     }
 };
 KernelTimer& timer(const char* which);
+// event timeline of one call (clb_set_timing(2)): tl_mark records a named event on a stream, clb_timeline formats the
+// offsets (ms from the first mark) after synchronising; for the step breakdowns under profiles/
+void tl_mark(const char* name, cudaStream_t s);
 
 // a growable device buffer
 struct DevBuf {

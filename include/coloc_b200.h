@@ -350,7 +350,9 @@ int  clb_microbench_mma(int device, double* out6);
 /* number of kernels this library launched on the calling process so far (bench's gpu_launches) */
 int64_t clb_launch_count(void);
 /* time of the last match kernel (ms, CUDA events on its own stream); 0 when timing is off */
-int  clb_set_timing(int on);
+int  clb_set_timing(int on);   /* 0 off, 1 per-kernel event pairs (clb_last_kernel_ms), 2 also named marks for clb_timeline */
+/* event timeline of the calls since the last clb_timeline (timing level 2): "name:ms name:ms ..." offsets from the first mark */
+int  clb_timeline(char* buf, int cap);
 /* Process-wide planning knobs (atomics; set them before the calls they should affect): "match_tc" (-1 auto: tensor-core
  * path from 2^24 comparisons up, 0 never, 1 always), "match_tc_chunks" / "match_chunks" (0 = auto), "match_rq" (0 auto, 1, 2, 4
  * queries per thread of the POPC kernel), "match_balance" (-1 the time model chooses, 0 uniform chunks, 1 balanced job list),
