@@ -6,4 +6,4 @@ host side for the reference is the C++ shim in coloc_b200/shim/coloc/ (see INTEG
 There is no CPU fallback: using `coloc_b200.api` without the built library raises.
 """
 from .api import (Detector, Matcher, ShardedMatcher, FrameStream, FeatureMap, is_lab, ClbError, KP_DTYPE, PARTIAL_DTYPE, PAIR_DTYPE, OBS_DTYPE, UNDEFINED_FEAT, lib, lib_path, build,  # noqa: F401
-                  launch_count, set_timing, timeline, last_kernel_ms, set_param, get_param, microbench_pipes, microbench_mma, PinnedArray, pinned_like)
+                  launch_count, set_timing, timeline, last_kernel_ms, set_param, get_param, microbench_pipes, microbench_mma, match_2nn_noalloc, PinnedArray, pinned_like)

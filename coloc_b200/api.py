@@ -156,6 +156,12 @@ def pinned_like(a):
     return h, h.array
 
 
+def match_2nn_noalloc(dQ, nQ, dT, nT, threshold, d_match, d_best=None, d_second=None, stream=None):
+    """clb_match_2nn_noalloc: allocation-free 2-NN on device pointers (static device scratch; nQ <= 32768).  stream None = legacy default"""
+    st = C.c_void_p(0) if stream is None else C.c_void_p(int(stream) if int(stream) != 0 else 1)
+    _check(lib().clb_match_2nn_noalloc(_dptr(dQ), int(nQ), _dptr(dT), int(nT), int(threshold), _dptr(d_match), _dptr(d_best), _dptr(d_second), st))
+
+
 def _sarg(stream):
     """cudaStream_t argument: None -> NULL (= the object's own stream); a torch stream handle of 0 (the legacy
     default stream) is passed as cudaStreamLegacy (0x1) so that it is not mistaken for NULL."""

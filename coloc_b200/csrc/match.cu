@@ -419,4 +419,74 @@ int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int thre
     return CLB_OK;
 }
 
+// ---- allocation-free entry point (clb_match_2nn_noalloc) ------------------------------------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the POPC sweep
+// (match_kernel<RQ, 2>) + merge_chunks_kernel with the per-chunk (best, second) key pairs -- the only scratch this path needs --
+// in a file-scope device array instead of the matcher object's cudaMalloc'ed buffer.  4 MiB, held by every GPU that loads the
+// library until the process exits.  In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address comes
+// from cudaGetSymbolAddress, once per device with that device current, and is what the kernels are given.
+static constexpr size_t NOALLOC_SCRATCH_BYTES = 4u << 20;
+static constexpr size_t NOALLOC_ENTRIES = NOALLOC_SCRATCH_BYTES / sizeof(uint2);       // 524 288 (chunk, query) slots
+static constexpr int NOALLOC_MAX_Q = 32768;                                            // leaves >= 16 chunks at the largest nQ
+static constexpr long long NOALLOC_MAX_T = 16ll * MT_MAX_CHUNK_ROWS;                   // 2^26 rows: 16 chunks of 2^22 rows at most
+static __device__ __align__(256) uint2 g_noalloc_scratch[NOALLOC_ENTRIES];
+
+static uint2* g_noalloc_ptr[64] = {nullptr};      // per device: address of the array ON that device
+static int g_noalloc_sms[64] = {0};
+
+int match_2nn_noalloc(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
+                      int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
+    if (nQ < 0 || nT < 0 || (nQ > 0 && (!dQ || !d_match)) || (nT > 0 && !dT)) { snprintf(g_err, sizeof(g_err), "bad descriptor set"); return CLB_EINVAL; }
+    if (nQ > NOALLOC_MAX_Q || (long long)nT > NOALLOC_MAX_T) {
+        snprintf(g_err, sizeof(g_err), "clb_match_2nn_noalloc: %d queries x %d rows exceed the static scratch (at most %d queries, %lld rows); "
+                 "use clb_match_2nn_dev", nQ, nT, NOALLOC_MAX_Q, NOALLOC_MAX_T);
+        return CLB_EINVAL;
+    }
+    if (nQ == 0) return CLB_OK;
+    if (((uintptr_t)dQ & 15) || ((uintptr_t)dT & 15)) { snprintf(g_err, sizeof(g_err), "descriptor pointers must be 16-byte aligned"); return CLB_EINVAL; }
+    int dev = 0;
+    CLB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { snprintf(g_err, sizeof(g_err), "device index %d out of range", dev); return CLB_EINVAL; }
+    if (!g_noalloc_ptr[dev]) {                     // set-up, once per device, with that device current
+        uint2* ptr = nullptr;
+        CLB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_scratch));
+        int sms = 0;
+        CLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g_noalloc_sms[dev] = sms > 0 ? sms : 148;
+        g_noalloc_ptr[dev] = ptr;
+    }
+    uint2* part = g_noalloc_ptr[dev];
+    // chunk plan of the POPC kernel, with the chunk count capped by what the static array holds for nQ queries
+    MatchPlan p = plan_match(nQ, nT, g_noalloc_sms[dev]);
+    const int fit = (int)(NOALLOC_ENTRIES / (size_t)nQ);                    // >= 16
+    if (p.nchunks > fit) {
+        int rpc = (nT + fit - 1) / fit;
+        rpc = (rpc + MT_TILE_ROWS - 1) / MT_TILE_ROWS * MT_TILE_ROWS;
+        p.rpc = rpc; p.nchunks = (nT + rpc - 1) / rpc;
+    }
+    if (p.rpc > MT_MAX_CHUNK_ROWS || (size_t)p.nchunks * (size_t)nQ > NOALLOC_ENTRIES || p.nchunks > 65535) {
+        snprintf(g_err, sizeof(g_err), "clb_match_2nn_noalloc: no chunk plan fits the static scratch for %d x %d", nQ, nT); return CLB_EINVAL;
+    }
+    // every (chunk, query) slot the merge reads is written by the sweep of THIS call: nothing has to start at zero, and what
+    // the previous call left in the array is never read
+    if (p.nchunks > 0) {
+        dim3 grid(p.qblocks, p.nchunks);
+        const uint4* Q4 = reinterpret_cast<const uint4*>(dQ);
+        const uint4* T4 = reinterpret_cast<const uint4*>(dT);
+        if (p.rq >= 4) match_kernel<4, 2><<<grid, MT_THREADS, 0, s>>>(Q4, nQ, T4, nT, p.rpc, part);
+        else if (p.rq == 2) match_kernel<2, 2><<<grid, MT_THREADS, 0, s>>>(Q4, nQ, T4, nT, p.rpc, part);
+        else match_kernel<1, 2><<<grid, MT_THREADS, 0, s>>>(Q4, nQ, T4, nT, p.rpc, part);
+        CLB_LAUNCHED();
+    }
+    merge_chunks_kernel<<<(nQ + 255) / 256, 256, 0, s>>>(part, p.nchunks, p.rpc, nQ, nT, 0ll, threshold, 0.f, d_match, d_best, d_second, nullptr);
+    CLB_LAUNCHED();
+    return CLB_OK;
+}
+
 }  // namespace clb
+
+extern "C" int clb_match_2nn_noalloc(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
+                                     int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream) {
+    // NULL = the legacy default stream (there is no object whose stream it could mean); cudaStreamLegacy / PerThread pass through
+    return clb::match_2nn_noalloc(dQ, nQ, dT, nT, threshold, d_match_out, d_best_out, d_second_out, (cudaStream_t)stream);
+}

@@ -163,6 +163,18 @@ int  clb_match_2nn(clb_matcher* m, const uint64_t* Q, int nQ, const uint64_t* T,
 int  clb_match_2nn_dev(clb_matcher* m, const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
                        int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
 
+/* Allocation-free 2-NN.  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as clb_match_2nn_dev
+ * (match[], best, second; margin test `second - best > threshold`), computed by the POPC sweep + chunk merge with the per-chunk
+ * scratch in a 4 MiB file-scope device array that every GPU loading the library holds until exit -- no matcher object, no
+ * cudaMalloc / cudaFree or other allocating call (the first call on a device only looks the array's address up).  Limits:
+ * nQ <= 32 768 and nT <= 2^26 rows; larger sizes return CLB_EINVAL (clb_last_error names the limit).  DEVICE pointers, 16-byte
+ * aligned; best / second outputs may be NULL; enqueue only, on `stream` (NULL = the legacy default stream).  Every call shares
+ * the one array (it keeps the last call's contents; every slot a call reads it has written itself, nothing needs clearing):
+ * calls that overlap on the GPU -- different streams, different threads -- race; order them on one stream or by events. */
+int  clb_match_2nn_noalloc(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int threshold,
+                           int32_t* d_match_out, int32_t* d_best_out, int32_t* d_second_out, void* stream);
+
 /* GPUMatcher::setMapData  GPUMatcher.hpp:110-117 (HOST pointer; H2D once per map) */
 int  clb_set_map(clb_matcher* m, const uint64_t* M, int nM);
 /* GPUMatcher::setQueryImage + matchFeaturesWithMap  GPUMatcher.hpp:130-141,252-271
