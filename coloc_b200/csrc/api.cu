@@ -3,6 +3,8 @@
 // (include/coloc/GPUDetector.hpp:70-155, GPUMatcher.hpp:70-108).
 #include "common.cuh"
 #include <string.h>
+#include <stdlib.h>
+#include <nvtx3/nvToolsExt.h>
 #include <map>
 #include <mutex>
 #include <string>
@@ -26,6 +28,10 @@ KernelTimer& timer(const char* which) {
     std::lock_guard<std::mutex> lk(g_timer_mu);
     return g_timers[which];
 }
+bool nvtx_on() { static const bool on = [] { const char* e = getenv("COLOC_B200_NVTX"); return e && *e && *e != '0'; }(); return on; }
+void nvtx_push(const char* name) { nvtxRangePushA(name); }
+void nvtx_pop() { nvtxRangePop(); }
+
 struct TlMark { std::string name; cudaEvent_t ev; };
 static std::vector<TlMark> g_tl;
 void tl_mark(const char* name, cudaStream_t s) {

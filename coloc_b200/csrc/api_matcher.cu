@@ -162,7 +162,7 @@ static int match_partial_streamed(clb_matcher* m, const uint64_t* dQ, int nQ, co
         m->pending.x_bytes = tc ? tc_t_bytes(rows) : 0; m->pending.x = tc ? m->sx[b].p : nullptr;
         rc = match_dispatch(m, dQ, nQ, m->sraw[b].as<uint64_t>(), rows, t_base + start, 0, 0.f, nullptr, nullptr, nullptr, parts + (size_t)k * nQ, s, Qx, Tx);
         if (rc) { m->pending.set = false; return rc; }
-        if (m->pending.set) { rc = clb_consume_pending(m, s); if (rc) return rc; }      // a path that launched nothing
+        if (m->pending.set || m->q_wait_set) { rc = clb_consume_pending(m, s); if (rc) return rc; }      // a path that launched nothing
         CLB_CUDA(cudaEventRecord(m->ev_rawfree[b], s));
         tl_mark("slice_swept", s);
         start += sz;
@@ -181,7 +181,7 @@ int clb_matcher_create(const clb_matcher_opts* opts, int device, clb_matcher** o
     if (!m) return CLB_ENOMEM;
     m->o = *opts; m->device = device; m->n_map = 0; m->mapx_valid = false; m->mapx_ver = 0; m->stream = nullptr;
     m->jobs_host = nullptr; m->jobs_host_cap = 0; m->jobs_ev_set = false; m->stream_ready = false; m->copy_stream = nullptr; m->ev_map_set = false;
-    m->pending.set = false;
+    m->pending.set = false; m->q_wait_set = false;
     cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, device);
     cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = m->q.reserve((size_t)opts->maxkp * 64);

@@ -320,7 +320,7 @@ int clb_sharded_match_map(clb_sharded* s, const uint64_t* Q, int nQ, int thresho
             CLB_CUDA(cudaMemcpyAsync(x0.q.p, src, qbytes, cudaMemcpyHostToDevice, s->up_stream));
             CLB_CUDA(cudaEventRecord(s->ev_up, s->up_stream));
             tl_mark("queries_uploaded", s->up_stream);
-            CLB_CUDA(cudaStreamWaitEvent(st, s->ev_up, 0));
+            x0.m->q_wait_ev = s->ev_up; x0.m->q_wait_set = true;      // the first sweep launch waits for it (matcher_priv.cuh)
         } else {
             CLB_CUDA(cudaMemcpyAsync(x0.q.p, src, qbytes, cudaMemcpyHostToDevice, st));
         }

@@ -62,6 +62,17 @@ KernelTimer& timer(const char* which);
 // offsets (ms from the first mark) after synchronising; for the step breakdowns under profiles/
 void tl_mark(const char* name, cudaStream_t s);
 
+// NVTX ranges around the stages (resize, fast, describe, expand, match, merge), behind COLOC_B200_NVTX=1 in the environment so
+// that a timeline tool shows the host side of every launch; nvtx3 is header-only and binds the tool's library at run time
+bool nvtx_on();
+void nvtx_push(const char* name);
+void nvtx_pop();
+struct NvtxRange {
+    bool on;
+    explicit NvtxRange(const char* name) : on(nvtx_on()) { if (on) nvtx_push(name); }
+    ~NvtxRange() { if (on) nvtx_pop(); }
+};
+
 // a growable device buffer
 struct DevBuf {
     void* p = nullptr; size_t cap = 0;

@@ -851,6 +851,7 @@ int fast_tile_box(int* w, int* h) { *w = Fast2<32, true>::SSTR; *h = Fast2<32, t
 // standalone = no resize kernel ran in front (stage-level entry point): the row counters are cleared here
 int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int quirk, void* scratch, size_t scratch_bytes,
                 clb_keypoint* d_kps, int cap, int* d_total, cudaStream_t s, bool pdl, bool standalone) {
+    NvtxRange nvtx_range("clb:fast");
     if (fast_scratch_bytes(lt) > scratch_bytes) { snprintf(g_err, sizeof(g_err), "fast scratch too small"); return CLB_EINVAL; }
     RowMap rm = make_rowmap(lt);
     const FastLayout lay = fast_layout(lt);

@@ -319,6 +319,7 @@ int launch_match(const uint64_t* dQ, int nQ, const uint64_t* dT, int nT, int64_t
                  void* scratch, size_t scratch_bytes, int sm_count,
                  int threshold, float ratio, int32_t* d_match, int32_t* d_best, int32_t* d_second,
                  clb_partial* d_partial, cudaStream_t s, const void* Qx, const void* Tx) {
+    NvtxRange nvtx_range("clb:match");
     if (nQ <= 0) return CLB_OK;
     if (((uintptr_t)dQ & 15) || ((uintptr_t)dT & 15)) { snprintf(g_err, sizeof(g_err), "descriptor pointers must be 16-byte aligned"); return CLB_EINVAL; }
     if (Tx && nT > 0) {
@@ -394,6 +395,7 @@ merge_jobs_kernel(const MergeJob* __restrict__ jobs, int threshold, float ratio)
 }
 
 int launch_merge_jobs(const MergeJob* d_jobs, int njobs, int max_nQ, int threshold, float ratio, cudaStream_t s) {
+    NvtxRange nvtx_range("clb:merge");
     if (njobs <= 0 || max_nQ <= 0) return CLB_OK;
     if (njobs > 65535) { snprintf(g_err, sizeof(g_err), "too many pairs in one list"); return CLB_EINVAL; }
     dim3 grid((max_nQ + 255) / 256, njobs);
@@ -413,6 +415,7 @@ int launch_fold_partials(const clb_partial* parts, int nparts, int nQ, clb_parti
 
 int launch_merge_partials(const clb_partial* parts, int nparts, int nQ, int threshold,
                           int32_t* d_match, int32_t* d_best, int32_t* d_second, cudaStream_t s) {
+    NvtxRange nvtx_range("clb:merge");
     if (nQ <= 0) return CLB_OK;
     merge_partials_kernel<<<(nQ + 255) / 256, 256, 0, s>>>(parts, nparts, nQ, threshold, d_match, d_best, d_second);
     CLB_LAUNCHED();

@@ -1274,6 +1274,7 @@ size_t tc_q_bytes(int nQ) { return (size_t)((nQ + TC_QROWS - 1) / TC_QROWS) * (t
 size_t tc_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * (tc_version() >= 3 ? TC3_TILE_BYTES : TC_TILE_BYTES); }
 
 int launch_expand(const uint64_t* d_rows, int n, size_t out_bytes, void* d_out, cudaStream_t s) {
+    NvtxRange nvtx_range("clb:expand");
     if (out_bytes == 0) return CLB_OK;
     const size_t chunks = out_bytes / 16;
     const size_t blocks = (chunks + 255) / 256;
@@ -1336,6 +1337,7 @@ bool tc_needs_qx() { return tc_version() == 1 || tc_version() == 3; }
 size_t tc4_t_bytes(int nT) { return (size_t)((nT + TC_TILE - 1) / TC_TILE) * TC3_TILE_BYTES; }
 
 int launch_expand4(const uint64_t* d_rows, int n, void* d_out, cudaStream_t s) {
+    NvtxRange nvtx_range("clb:expand");
     const size_t chunks = tc4_t_bytes(n) / 16;
     if (chunks == 0) return CLB_OK;
     const size_t blocks = (chunks + 255) / 256;
@@ -1388,6 +1390,7 @@ double tc_balanced_cost_us(long long units, long long strips, int sm_count, long
 }
 
 int launch_match_tc_jobs(const TcJob* d_jobs, int njobs, cudaStream_t s) {
+    NvtxRange nvtx_range("clb:match");
     if (njobs <= 0) return CLB_OK;
     static bool attr_done[64] = {false};
     int dev = 0;

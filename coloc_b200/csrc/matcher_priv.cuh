@@ -28,10 +28,20 @@ struct clb_matcher {
     // deferred head of a streamed slice's sweep: "wait for the slice copy, expand it" is enqueued by the sweep's launch path
     // AFTER its job-table upload, so that the small upload is not parked behind the wait (see match_partial_streamed)
     struct Pending { bool set; cudaEvent_t ev; const uint64_t* raw; int rows; size_t x_bytes; void* x; } pending;
+    // an event the NEXT sweep launch must wait for (the query upload of clb_sharded_match_map on its own stream): waited for in
+    // the launch path, not at call entry, so that the copy stream's entry event -- and with it the first DB slice -- is not
+    // ordered behind that upload
+    cudaEvent_t q_wait_ev;
+    bool q_wait_set;
 };
 
 // enqueue a pending slice head on `s` (no-op when none is pending)
 inline int clb_consume_pending(clb_matcher* m, cudaStream_t s) {
+    if (m->q_wait_set) {
+        m->q_wait_set = false;
+        cudaError_t e = cudaStreamWaitEvent(s, m->q_wait_ev, 0);
+        if (e != cudaSuccess) return clb::set_cuda_error(e, "cudaStreamWaitEvent", __FILE__, __LINE__);
+    }
     if (!m->pending.set) return CLB_OK;
     m->pending.set = false;
     cudaError_t e = cudaStreamWaitEvent(s, m->pending.ev, 0);

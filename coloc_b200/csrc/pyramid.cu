@@ -203,6 +203,7 @@ int launch_resize_tables(const LevelTable& lt, const ResizePlan& rp, uint2* d_ta
 }
 
 int launch_resize(const LevelTable& lt, const ResizePlan& rp, const LevelMaps& maps, uint32_t* clear, int clear_words, cudaStream_t s, bool pdl) {
+    NvtxRange nvtx_range("clb:resize");
     int smem = 0;
     const int tiles = lt.n > 1 ? rp.tile_base[lt.n] : 0;
     for (int L = 1; L < lt.n; ++L) {
