@@ -301,7 +301,10 @@ def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, wor
     keypoints + descriptors come back to pinned host memory and, with_match, each rank matches consecutive frames of its
     sub-stream on the device (descriptors never leave it) and reads the match list back.  At the end ONE NCCL gather moves the
     per-frame (keypoint count, match count) table and the match lists to rank 0.  Wall clock from a common barrier to the
-    slowest rank's last result, everything included; frames/s = nframes / that."""
+    slowest rank's last result, everything included; frames/s = nframes / that.
+    The synthetic stream has `distinct` = 4 different views (20.7 k / 14.7 k / 19.3 k / 14.5 k keypoints at 1280 x 720); frame k shows
+    view (k // world) % 4, so that every rank sees the same mix of views whatever the rank count -- with view k % 4 and 2 / 4 / 8
+    ranks, rank 0 would only ever get the heaviest views and the slowest-rank clock would measure that artefact (83 % "efficiency")."""
     pins = []
     views, _ = synth.config_views(w, h, distinct)            # consecutive frames see the same scene (matches exist)
     for i in range(distinct):
@@ -330,7 +333,7 @@ def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, wor
         pending = None                      # (buffer index, rows, local frame) of the match list still in flight
         while done < n:
             while sub < n and fs.in_flight() < INFLIGHT:
-                fs.submit(pins[frames[sub] % distinct].numpy(), tag=sub); sub += 1
+                fs.submit(pins[(frames[sub] // world) % distinct].numpy(), tag=sub); sub += 1
             tag, k, d, dk, dd, cnt = fs.next(copy=False)
             nk += cnt
             if record:
@@ -633,7 +636,8 @@ def run_ours(args, rank, world, local_rank):
     cfgs = [("c2_stream_detect_describe", (1280, 720, 256, False)), ("c2_stream_detect_describe_match", (1280, 720, 256, True)),
             ("c5_stream_detect_describe_match", (3840, 2160, 256, True))]
     if world > 1:      # 256 frames over 8 ranks are 32 frames per pipeline: the same streams `world` times longer show the rate without fill / drain
-        cfgs += [("c2_stream_detect_describe_match_long", (1280, 720, 256 * world, True)), ("c5_stream_detect_describe_match_long", (3840, 2160, 256 * world, True))]
+        cfgs += [("c2_stream_detect_describe_long", (1280, 720, 256 * world, False)), ("c2_stream_detect_describe_match_long", (1280, 720, 256 * world, True)),
+                 ("c5_stream_detect_describe_match_long", (3840, 2160, 256 * world, True))]
     for key, a in cfgs:
         ok = 1
         try:
@@ -716,6 +720,7 @@ def run_ours(args, rank, world, local_rank):
                        "nQ": NQ, "nT": NT, "threshold": THRESH, "parallelism": f"db-rows x{world}",
                        "api": "clb_sharded_* (C ABI, rank mode): sweep + ncclAllGather of nQ x 16 B per rank + merge inside the library",
                        "l2": "256 MiB device fill between steps, outside the per-step event pairs",
+                       "host_cores_per_rank": len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None,
                        "planted_match_recall": recovered, "oracle_slice_equal": oracle_slice,
                        "oracle_slice": "queries 1000..1063 of the sharded result (match, best, second) == oracle scan of all 2 M rows",
                        "e2e_equals_resident": e2e_same,
@@ -760,6 +765,19 @@ def run_ours(args, rank, world, local_rank):
     emit(json.dumps(line))
 
 
+def pin_rank_to_cores(local_rank, world):
+    """one block of host cores per rank.  Every rank spins on its stream syncs and brings NCCL / CUDA helper threads; left to the
+    scheduler on the box's 24 vCPUs they land on each other's cores (measured with two independent single-GPU processes:
+    6 990 frames/s each when pinned to disjoint cores, down to 86 frames/s on a 4K stream unpinned -- tools/stream_pair_probe.py)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // world)
+        mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        os.sched_setaffinity(0, mine)
+    except (AttributeError, OSError):
+        pass
+
+
 _REAL_STDOUT = None
 
 
@@ -782,6 +800,9 @@ def emit(text):
 
 
 def main():
+    # frame streams keep 3-5 frames in flight on their own CUDA streams next to the matcher's, torch's and NCCL's: with the default
+    # 8 hardware work queues they alias onto each other and serialise (must be set before the CUDA context exists)
+    os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
     guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -794,6 +815,8 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
+    if world > 1:
+        pin_rank_to_cores(local_rank, world)
     if world > 1:
         import torch
         import torch.distributed as dist
