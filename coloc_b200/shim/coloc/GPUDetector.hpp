@@ -111,6 +111,16 @@ public:
         return EXIT_SUCCESS;
     }
 
+    // GPUDetector.hpp:188-212 (`#ifdef USE_STREAM`, a ROS topic frame).  The reference takes a cv_bridge::CvImagePtr; any pointer-like
+    // object whose `->image` has `data`, `cols`, `rows` (cv::Mat's members) works here, so the shim needs neither ROS nor OpenCV.
+    // The reference's copy of the packing loop writes `scale * x` into BOTH coordinates (:203, a typo: detectFeaturesFile :175-176
+    // has x, y); this method packs x, y like detectFeaturesFile.
+    template <class ImagePtr>
+    void detectFeaturesTopic(uint8_t idx, coloc::FeatureMap& regions, ImagePtr imagePtr) {
+        detectFeaturesBuffer(idx, regions, static_cast<const uint8_t*>(imagePtr->image.data), (int)imagePtr->image.cols,
+                             (int)imagePtr->image.rows);
+    }
+
 private:
     // GPUDetector.hpp:216-291: H2D, pyramid, FAST+NMS+angle, LATCH, D2H -- one ABI call
     // The results land in page-locked scratch that lives as long as the detector (the describe kernel writes the descriptors

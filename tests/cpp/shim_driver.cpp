@@ -3,7 +3,9 @@
 // computeMatches over the FeatureMap, setMapData + matchSceneWithMap.  Dumps raw results for the python test.
 // Build: g++ -std=c++14 -DCLB_SHIM_STANDALONE -Iinclude -Icoloc_b200/shim tests/cpp/shim_driver.cpp -Lcoloc_b200 -lcoloc_b200
 #include <cstdio>
+#include <cstring>
 #include <string>
+#include <vector>
 #include "coloc/GPUDetector.hpp"
 #include "coloc/GPUMatcher.hpp"
 
@@ -43,6 +45,23 @@ int main(int argc, char** argv) {
     if (detector.detectFeaturesFile(1, regions, b) != EXIT_SUCCESS) return 3;
     dump(f, detector.kps); dump(f, detector.desc);
     dump(f, regions[0]->Features());
+    {   // a ROS-topic style frame (GPUDetector.hpp:188-212): same bytes as file b through detectFeaturesTopic
+        std::vector<unsigned char> px; int pw = 0, ph = 0;
+        if (FILE* g = fopen(b.c_str(), "rb")) {
+            int maxv = 0;
+            if (fscanf(g, "P5 %d %d %d", &pw, &ph, &maxv) == 3 && fgetc(g) != EOF) { px.resize((size_t)pw * ph); if (fread(px.data(), 1, px.size(), g) != px.size()) px.clear(); }
+            fclose(g);
+        }
+        if (px.empty()) return 6;
+        struct Img { unsigned char* data; int cols, rows; };
+        struct Msg { Img image; } msg{{px.data(), pw, ph}};
+        detector.detectFeaturesTopic(2, regions, &msg);
+        if (regions[2]->RegionCount() != regions[1]->RegionCount() ||
+            memcmp(regions[2]->DescriptorRawData(), regions[1]->DescriptorRawData(), regions[1]->RegionCount() * 64) != 0) return 6;
+        for (size_t i = 0; i < regions[1]->RegionCount(); ++i)
+            if (regions[2]->Features()[i].x() != regions[1]->Features()[i].x() || regions[2]->Features()[i].y() != regions[1]->Features()[i].y()) return 6;
+        regions.erase(2);
+    }
     openMVG::matching::PairWiseMatches putative;
     if (matcher.computeMatches(regions, putative) != EXIT_SUCCESS) return 4;
     dump(f, putative[{0, 1}]);
