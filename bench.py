@@ -721,6 +721,7 @@ def run_ours(args, rank, world, local_rank):
                        "api": "clb_sharded_* (C ABI, rank mode): sweep + ncclAllGather of nQ x 16 B per rank + merge inside the library",
                        "l2": "256 MiB device fill between steps, outside the per-step event pairs",
                        "host_cores_per_rank": len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else None,
+                       "cpu_affinity": dict(_AFFINITY),
                        "planted_match_recall": recovered, "oracle_slice_equal": oracle_slice,
                        "oracle_slice": "queries 1000..1063 of the sharded result (match, best, second) == oracle scan of all 2 M rows",
                        "e2e_equals_resident": e2e_same,
@@ -765,15 +766,57 @@ def run_ours(args, rank, world, local_rank):
     emit(json.dumps(line))
 
 
+_AFFINITY = {"mode": "unpinned"}
+
+
+def _nvml_device_cpus(world):
+    """CPUs NVML calls local to each of the job's GPUs (nvmlDeviceGetCpuAffinity: the cores of the GPU's NUMA node), or None when
+    NVML has nothing to say.  NVML numbers devices in PCI order, which is CUDA's order on a homogeneous box; CUDA_VISIBLE_DEVICES
+    (a list of indices) is honoured."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        idx = [int(t) for t in vis.split(",")] if vis and all(t.strip().isdigit() for t in vis.split(",")) else list(range(world))
+        if len(idx) < world:
+            return None
+        ncpu = (os.cpu_count() or 64)
+        words = (ncpu + 63) // 64
+        out = []
+        for r in range(world):
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx[r])
+            mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+            out.append({64 * wi + b for wi, wv in enumerate(mask) for b in range(64) if (int(wv) >> b) & 1})
+        return out
+    except Exception:       # noqa: BLE001 -- no NVML, no permission, a VM that hides the topology: fall back to plain blocks
+        return None
+
+
 def pin_rank_to_cores(local_rank, world):
     """one block of host cores per rank.  Every rank spins on its stream syncs and brings NCCL / CUDA helper threads; left to the
-    scheduler on the box's 24 vCPUs they land on each other's cores (measured with two independent single-GPU processes:
-    6 990 frames/s each when pinned to disjoint cores, down to 86 frames/s on a 4K stream unpinned -- tools/stream_pair_probe.py)."""
+    scheduler on the box's vCPUs they land on each other's cores (measured with two independent single-GPU processes:
+    6 990 frames/s each when pinned to disjoint cores, down to 86 frames/s on a 4K stream unpinned -- tools/stream_pair_probe.py).
+    Where NVML reports different CPU sets for the job's GPUs (a multi-socket host), a rank's block is cut out of ITS GPU's set, so
+    that the page-locked buffers it allocates afterwards (first touch) and its copies stay on the GPU's NUMA node."""
     try:
         cores = sorted(os.sched_getaffinity(0))
         per = max(1, len(cores) // world)
         mine = cores[local_rank * per:(local_rank + 1) * per] or cores
+        mode = "blocks"
+        local = _nvml_device_cpus(world)
+        if local:
+            sets = [frozenset(c & set(cores)) for c in local]
+            if all(sets) and len(set(sets)) > 1:                      # the topology has structure and every GPU has usable cores
+                peers = [r for r in range(world) if sets[r] == sets[local_rank]]
+                pool = sorted(sets[local_rank])
+                share = max(1, len(pool) // len(peers))
+                k = peers.index(local_rank)
+                cut = pool[k * share:(k + 1) * share]
+                if len(cut) >= max(1, per // 2):                      # never accept a much smaller block than the plain scheme gives
+                    mine, mode = cut, "nvml-numa"
         os.sched_setaffinity(0, mine)
+        _AFFINITY.update({"mode": mode, "cpus": f"{mine[0]}-{mine[-1]}" if mine == list(range(mine[0], mine[-1] + 1)) else ",".join(map(str, mine)),
+                          "n": len(mine)})
     except (AttributeError, OSError):
         pass
 

@@ -449,20 +449,26 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ L
     const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * TH;
     const int tid = threadIdx.x, lane = tid & 31;
 
+    // Which grid is in front of this one?  Without quirk levels it is the resize kernel: wait for it.  With quirk levels it is
+    // fast_xend_kernel, every CTA of which sat out the resize kernel (griddepcontrol.wait) BEFORE releasing its dependents: by the
+    // time this grid exists the levels are complete and visible, so only the tiles of a quirk level -- which read xend[] -- have to
+    // wait for that grid itself.  The ~11 us latency-bound scan-end pass then runs next to the level-0 tiles instead of in front.
+    const bool lvl_quirk = (rm.quirk_mask >> L) & 1u;
+    const bool need_wait = rm.quirk_mask == 0u || lvl_quirk;
     if (TMA && tid == 0) {
         ptx_mbar_init(&bar, 1);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        ptx_grid_dep_wait();            // the level is written by the resize kernel in front of this one
+        if (need_wait) ptx_grid_dep_wait();            // the level is written by the resize kernel in front of this one
         ptx_mbar_expect_tx(&bar, (uint32_t)(F::SH * F::SSTR));
         ptx_tma_load_2d(px, &maps.fast[L], x0 - F::XO, y0 - 4, &bar);
     }
     ptx_grid_dep_launch();
     if (tid == 0) { n1 = 0; n2 = 0; }
     if (tid < TH) rowcnt[tid] = 0;
-    if (!TMA || ((rm.quirk_mask >> L) & 1u)) ptx_grid_dep_wait();      // xend[] comes from the kernel in front as well
+    if (!TMA || lvl_quirk) ptx_grid_dep_wait();      // xend[] comes from the kernel in front as well
     if (tid < F::CH) {                 // scan end of each score-region row: w - 3, or the reference's column walk (fast_xend_kernel)
         const int gy = y0 - 1 + tid;
-        s_xlim[tid] = (((rm.quirk_mask >> L) & 1u) && gy >= 3 && gy < h - 3) ? __ldg(xend + rm.row_base[L] + gy) : w - 3;
+        s_xlim[tid] = (((rm.quirk_mask >> L) & 1u) && gy >= 3 && gy < h - 3) ? __ldcg(xend + rm.row_base[L] + gy) : w - 3;
     }
     for (int i = tid; i < F::CH * F::CSTR / 4; i += 256) reinterpret_cast<uint32_t*>(sc)[i] = 0u;
     for (int i = tid; i < TH * FT_TW / 4; i += 256) reinterpret_cast<uint32_t*>(so)[i] = 0u;
