@@ -361,13 +361,19 @@ def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, wor
     run(mine[:min(8, len(mine))], False)
     torch.cuda.synchronize()
     if world > 1:                                        # NCCL sets its send / recv channels up on first use: not part of a frame stream
-        wt = torch.zeros(8, dtype=torch.int32, device=dev)
-        dist.gather(wt, [torch.empty_like(wt) for _ in range(world)] if rank == 0 else None, dst=0)
+        # ... and torch loads its kernels lazily: the first torch.stack of gathered pieces cost rank 0 6.4 ms inside the first
+        # timed stream of the process (frames done at 18.5 ms, wall clock 24.9 ms at 2 GPUs); run the same tail once, untimed
+        wt = torch.zeros((nloc, 2), dtype=torch.int32).to(dev)
+        wg = [torch.empty_like(wt) for _ in range(world)] if rank == 0 else None
+        dist.gather(wt, wg, dst=0)
         torch.cuda.synchronize()
+        if rank == 0:
+            torch.stack(wg).cpu().numpy()
         dist.barrier()
     t0 = time.perf_counter()
     nk, ncmp, nm = run(mine, True)
     torch.cuda.synchronize()
+    t_run = time.perf_counter() - t0                     # this rank's frames done; the rest of the wall clock is the gather (and waiting for the slowest rank)
     gathered = None
     if world > 1:                                        # the one exchange: per-frame counts (+ match lists) to rank 0
         tab_d = table.to(dev)
@@ -380,14 +386,16 @@ def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, wor
         if rank == 0:
             gathered = torch.stack(gt).cpu().numpy()
     dt = time.perf_counter() - t0
-    tm = torch.tensor([dt, float(nk), float(ncmp), float(nm)], dtype=torch.float64, device=dev)
+    tm = torch.tensor([dt, float(nk), float(ncmp), float(nm), t_run, -t_run], dtype=torch.float64, device=dev)
+    run_max = run_min = t_run
     if world > 1:
         mx = tm.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
         dist.all_reduce(tm, op=dist.ReduceOp.SUM)
-        dt = float(mx[0].item())
+        dt = float(mx[0].item()); run_max = float(mx[4].item()); run_min = -float(mx[5].item())
     nk, ncmp, nm = float(tm[1].item()), float(tm[2].item()), float(tm[3].item())
     res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": INFLIGHT, "ranks": world, "keypoints_per_frame": nk / nframes,
            "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt, "wall_ms": dt * 1e3,
+           "frames_done_ms": {"slowest_rank": run_max * 1e3, "fastest_rank": run_min * 1e3},     # the remainder of wall_ms is the gather
            "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0),
            "dealing": "frame k -> rank k % world; each rank matches consecutive frames of its own sub-stream",
            "exchange": ("one NCCL gather of the per-frame (keypoints, matches) table" + (" and the match lists" if with_match else "") + " to rank 0") if world > 1 else "none"}
