@@ -370,31 +370,43 @@ def stream_extra(clb, torch, dist, synth, w, h, nframes, with_match, rank=0, wor
         if rank == 0:
             torch.stack(wg).cpu().numpy()
         dist.barrier()
-    t0 = time.perf_counter()
-    nk, ncmp, nm = run(mine, True)
-    torch.cuda.synchronize()
-    t_run = time.perf_counter() - t0                     # this rank's frames done; the rest of the wall clock is the gather (and waiting for the slowest rank)
+    # The stream is timed REPS times over the same frames and the MEDIAN run is reported (all wall clocks are kept in `wall_ms_runs`):
+    # at 8 ranks a 256-frame stream lasts 6 - 25 ms on a host with 4 vCPUs per rank, and one descheduled helper thread on one rank
+    # moves the slowest-rank clock by a third (measured: frames done after 7.5 ms on the fastest rank, 12.8 ms on the slowest).
+    REPS = 3
+    runs = []
     gathered = None
-    if world > 1:                                        # the one exchange: per-frame counts (+ match lists) to rank 0
-        tab_d = table.to(dev)
-        gt = [torch.empty_like(tab_d) for _ in range(world)] if rank == 0 else None
-        dist.gather(tab_d, gt, dst=0)
-        if with_match:
-            gl = [torch.empty_like(lists) for _ in range(world)] if rank == 0 else None
-            dist.gather(lists, gl, dst=0)
+    for rep in range(REPS):
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        nk, ncmp, nm = run(mine, True)
         torch.cuda.synchronize()
-        if rank == 0:
-            gathered = torch.stack(gt).cpu().numpy()
-    dt = time.perf_counter() - t0
-    tm = torch.tensor([dt, float(nk), float(ncmp), float(nm), t_run, -t_run], dtype=torch.float64, device=dev)
-    run_max = run_min = t_run
-    if world > 1:
-        mx = tm.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tm, op=dist.ReduceOp.SUM)
-        dt = float(mx[0].item()); run_max = float(mx[4].item()); run_min = -float(mx[5].item())
+        t_run = time.perf_counter() - t0                 # this rank's frames done; the rest of the wall clock is the gather (and waiting for the slowest rank)
+        if world > 1:                                    # the one exchange: per-frame counts (+ match lists) to rank 0
+            tab_d = table.to(dev)
+            gt = [torch.empty_like(tab_d) for _ in range(world)] if rank == 0 else None
+            dist.gather(tab_d, gt, dst=0)
+            if with_match:
+                gl = [torch.empty_like(lists) for _ in range(world)] if rank == 0 else None
+                dist.gather(lists, gl, dst=0)
+            torch.cuda.synchronize()
+            if rank == 0:
+                gathered = torch.stack(gt).cpu().numpy()
+        dt = time.perf_counter() - t0
+        tm = torch.tensor([dt, float(nk), float(ncmp), float(nm), t_run, -t_run], dtype=torch.float64, device=dev)
+        run_max = run_min = t_run
+        if world > 1:
+            mx = tm.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tm, op=dist.ReduceOp.SUM)
+            dt = float(mx[0].item()); run_max = float(mx[4].item()); run_min = -float(mx[5].item())
+        runs.append((dt, run_max, run_min, tm))
+    order = sorted(range(REPS), key=lambda r: runs[r][0])
+    dt, run_max, run_min, tm = runs[order[REPS // 2]]
     nk, ncmp, nm = float(tm[1].item()), float(tm[2].item()), float(tm[3].item())
     res = {"frame": f"{w}x{h}", "frames": nframes, "in_flight": INFLIGHT, "ranks": world, "keypoints_per_frame": nk / nframes,
            "frames_per_s": nframes / dt, "keypoints_per_s": nk / dt, "wall_ms": dt * 1e3,
+           "wall_ms_runs": [round(r[0] * 1e3, 3) for r in runs], "reported": "median of 3 runs over the same frames",
            "frames_done_ms": {"slowest_rank": run_max * 1e3, "fastest_rank": run_min * 1e3},     # the remainder of wall_ms is the gather
            "h2d_bytes_per_frame": w * h, "d2h_bytes_per_frame": int(84 * nk / nframes) + (4 * int(nk / nframes) if with_match else 0),
            "dealing": "frame k -> rank k % world; each rank matches consecutive frames of its own sub-stream",

@@ -44,6 +44,7 @@ struct RowMap {   // global row index <-> (level, y); for the v2 score kernel al
     int n; int row_base[CLB_MAX_LEVELS + 1];
     int tile_base[CLB_MAX_LEVELS + 1];      // first tile of each level for the tile height of this launch (host-computed:
     int tiles_x[CLB_MAX_LEVELS];            // the kernel's level search is compares only, no divisions per thread)
+    uint32_t tiles_x_magic[CLB_MAX_LEVELS]; // tile / tiles_x == umulhi(tile, magic) (0: divide); entries of tile_base above n are INT_MAX
     int bm_words;                           // words per row of the (row, 64-px tile) occupancy bitmap
     uint32_t quirk_mask;                    // bit L: level L takes its per-row scan end from xend[] (KFAST.h:243 edge)
 };
@@ -440,13 +441,21 @@ fast_nms2_kernel(const LevelTable lt, const RowMap rm, const __grid_constant__ L
     __shared__ uint16_t q1[F::NPOS], q2[F::NPOS];
     __shared__ int n1, n2, rowcnt[TH], s_xlim[F::CH];
 
-    int L = 0;
-    while (L + 1 < rm.n && (int)blockIdx.x >= rm.tile_base[L + 1]) ++L;
-    const int tile = blockIdx.x - rm.tile_base[L], tx_n = rm.tiles_x[L];
-    if ((int)blockIdx.x >= rm.tile_base[rm.n]) return;
+    // tile -> (level, tile row, tile column): four-step search of the largest L with tile_base[L] <= blockIdx.x (entries above the
+    // level count are INT_MAX) and a multiply-shift for the division -- this decode was 8 % of the kernel's instructions as a loop
+    // plus an integer division, executed by ~12 700 short-lived CTAs per 4K frame
+    const int bx = (int)blockIdx.x;
+    int L = bx >= rm.tile_base[8] ? 8 : 0;
+    L += bx >= rm.tile_base[L + 4] ? 4 : 0;
+    L += bx >= rm.tile_base[L + 2] ? 2 : 0;
+    L += bx >= rm.tile_base[L + 1] ? 1 : 0;
+    if (L >= rm.n) return;
+    const int tile = bx - rm.tile_base[L], tx_n = rm.tiles_x[L];
+    const uint32_t magic = rm.tiles_x_magic[L];
     const int w = lt.w[L], h = lt.h[L], stride = lt.stride[L];
     const uint8_t* __restrict__ img = lt.img[L];
-    const int x0 = (tile % tx_n) * FT_TW, y0 = (tile / tx_n) * TH;
+    const int tyi = magic ? (int)__umulhi((uint32_t)tile, magic) : tile / tx_n;
+    const int x0 = (tile - tyi * tx_n) * FT_TW, y0 = tyi * TH;
     const int tid = threadIdx.x, lane = tid & 31;
 
     // Which grid is in front of this one?  Without quirk levels it is the resize kernel: wait for it.  With quirk levels it is
@@ -829,8 +838,23 @@ static RowMap make_rowmap(const LevelTable& lt) {
     RowMap rm; rm.n = lt.n; rm.row_base[0] = 0; rm.bm_words = 0; rm.quirk_mask = 0;
     for (int i = 0; i < lt.n; ++i) rm.row_base[i + 1] = rm.row_base[i] + lt.h[i];
     for (int i = 0; i <= CLB_MAX_LEVELS; ++i) rm.tile_base[i] = 0;
-    for (int i = 0; i < CLB_MAX_LEVELS; ++i) rm.tiles_x[i] = 0;
+    for (int i = 0; i < CLB_MAX_LEVELS; ++i) { rm.tiles_x[i] = 0; rm.tiles_x_magic[i] = 0u; }
     return rm;
+}
+
+// tile grid of the v2 score kernel for tile height `th`: tile_base[] (INT_MAX above the level count: the kernel's level search
+// reads all 17 entries), tiles per row and the multiply-shift constant of the division by it.  floor(t * ceil(2^32 / d) / 2^32) ==
+// t / d for every t with t * d < 2^32 (the error term t * (d - 2^32 mod d) / (d * 2^32) stays below 1 / d); otherwise the kernel divides.
+static void fill_tile_grid(RowMap& rm, const LevelTable& lt, int th) {
+    rm.tile_base[0] = 0;
+    for (int L = 0; L < lt.n; ++L) {
+        const int txn = (lt.w[L] + FT_TW - 1) / FT_TW, tyn = (lt.h[L] + th - 1) / th;
+        rm.tiles_x[L] = txn;
+        rm.tile_base[L + 1] = rm.tile_base[L] + txn * tyn;
+        const unsigned long long tiles = (unsigned long long)txn * (unsigned long long)tyn;
+        rm.tiles_x_magic[L] = (txn > 1 && tiles * (unsigned long long)txn < 0x100000000ull) ? (uint32_t)(0x100000000ull / (unsigned long long)txn) + 1u : 0u;
+    }
+    for (int L = lt.n + 1; L <= CLB_MAX_LEVELS; ++L) rm.tile_base[L] = 0x7FFFFFFF;
 }
 
 // widths on which the compiled reference's `1 << 32` (KFAST.h:243) can drop a row's last 32 columns
@@ -895,10 +919,7 @@ int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int qui
             {{fast_nms2_kernel<16, 6, false, false>, fast_nms2_kernel<16, 6, true, false>}, {fast_nms2_kernel<16, 8, false, false>, fast_nms2_kernel<16, 8, true, false>}},
             {{fast_nms2_kernel<32, 6, false, false>, fast_nms2_kernel<32, 6, true, false>}, {fast_nms2_kernel<32, 8, false, false>, fast_nms2_kernel<32, 8, true, false>}}};
         const int big = (fvar & 4) ? 1 : 0, th = big ? 32 : 16;
-        for (int L = 0; L < lt.n; ++L) {
-            rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
-            rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + th - 1) / th);
-        }
+        fill_tile_grid(rm, lt, th);
         const int ntiles = rm.tile_base[lt.n];
         k2_t kern = fvar == 55 ? (k2_t)fast_nms2_kernel<32, 6, true, true> : k2[big][(fvar & 8) ? 1 : 0][(fvar & 16) ? 1 : 0];   // 55 = the product kernel (TMA-staged)
         CLB_CUDA(launch_ex(kern, dim3(ntiles), dim3(256), 0, s, pdl, lt, rm, maps, thresh, nms, fnms, row_count, use_bm ? bitmap : (uint32_t*)nullptr, (const int*)xend));
@@ -921,10 +942,7 @@ int launch_fast(const LevelTable& lt, const LevelMaps& maps, int thresh, int qui
         CLB_LAUNCHED();
     }
 #else
-    for (int L = 0; L < lt.n; ++L) {
-        rm.tiles_x[L] = (lt.w[L] + FT_TW - 1) / FT_TW;
-        rm.tile_base[L + 1] = rm.tile_base[L] + rm.tiles_x[L] * ((lt.h[L] + 31) / 32);
-    }
+    fill_tile_grid(rm, lt, 32);
     CLB_CUDA(launch_ex(fast_nms2_kernel<32, 6, true, true>, dim3(rm.tile_base[lt.n]), dim3(256), 0, s, pdl, lt, rm, maps, thresh, nms, 1, row_count, bitmap, (const int*)xend));
     CLB_LAUNCHED();
     CLB_CUDA(launch_ex(compact2_kernel, dim3(((int)rows + 7) / 8), dim3(256), 0, s, pdl, lt, rm, (const uint8_t*)nms, (const int*)row_count, d_kps, cap, d_total, (const uint32_t*)bitmap));
