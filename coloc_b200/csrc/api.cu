@@ -279,6 +279,11 @@ int clb_microbench_mma(int device, double* out6) {
     return microbench_mma(out6);
 }
 
+#ifdef CLB_LAB
+// lab library only (not in include/coloc_b200.h): per-tile clocks of CTA (0, 0) of the last sweep run with match_tc_dbg = 7
+int clb_lab_tile_clocks(long long* out1024) { return out1024 ? tc_lab_tile_clocks(out1024) : CLB_EINVAL; }
+#endif
+
 int clb_detector_create(const clb_detector_opts* opts, int device, clb_detector** out) {
     if (!opts || !out) return CLB_EINVAL;
     if (opts->scale_levels < 1 || opts->scale_levels > CLB_MAX_LEVELS || opts->width < 1 || opts->height < 1 ||

@@ -230,6 +230,9 @@ int launch_sincos(const float* d_a, int n, float* d_s, float* d_c, cudaStream_t 
 int latch_init();   // uploads the triplet table
 // microbench.cu
 int microbench_pipes(double* out8);
+#ifdef CLB_LAB
+int tc_lab_tile_clocks(long long* out1024);      // lab build: per-tile clocks of CTA (0, 0) of the last match_tc_dbg = 7 sweep
+#endif
 int microbench_mma(double* out6);      // match_tc.cu: bare tcgen05.mma kind::mxf4 stream on every SM
 
 }  // namespace clb

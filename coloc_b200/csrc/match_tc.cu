@@ -796,6 +796,12 @@ match_tc3_kernel(const uint8_t* __restrict__ Qx, int nQ, const uint8_t* __restri
 
 #endif   // CLB_LAB (v3 kernel)
 
+#ifdef CLB_LAB
+// match_tc_dbg = 7: per-tile clocks of CTA (0, 0) -- [0][j] DB K-block pair of tile j issued by the TMA warp, [1][j] MMAs of tile j
+// issued (query tile 0), [2][j] accumulator j seen by epilogue warp 0, [3][j] epilogue warp 0 done with tile j (clb_lab_tile_clocks)
+__device__ long long g_tc_trace[6][256];     // [4][j] TMEM loads of tile j landed, [5][j] first 32 columns processed
+#endif
+
 // ---- v4: v3 with the query tiles in TMEM (TS mode) and 16 epilogue warps --------------------------------
 // tools/tc_dbg.py on v3: 5.4 T cmp/s, 6.1 T with the epilogue's TMEM reads disabled -- the scan of 128 distances per
 // thread per tile had become the long pole.  Here every accumulator row is shared by two threads (64 columns each),
@@ -824,10 +830,12 @@ __device__ __forceinline__ void tc_mma_mxf4_ts_n64(uint32_t d_tmem, uint32_t a_t
 }
 
 template <bool MASKED>
-__device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcStateF& st) {
+__device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0, int valid, uint32_t bar_release, int lane, TcStateF& st,
+                                                      long long* tr = nullptr) {      // tr: lab trace (clocks after the TMEM loads landed / after the first 32 columns)
     float v0[32], v1[32];
     tc_ld32(t, v0); tc_ld32(t + 32, v1);
     tc_wait_ld();
+    if (tr) tr[0] = clock64();
     tc_fence_before();
     __syncwarp();
     if (lane == 0) tc_mbar_arrive(bar_release);
@@ -839,6 +847,7 @@ __device__ __forceinline__ void tc_epilogue_half_tile(uint32_t t, uint32_t row0,
         }
     }
     tc_process32f(v0, row0, st);
+    if (tr) tr[256] = clock64();
     tc_process32f(v1, row0 + 32, st);
 }
 
@@ -913,6 +922,9 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
             if (tc_elect_one()) {
                 tc_mbar_expect_tx(bar_full + 8 * s, TC_KB_BYTES);
                 tc_bulk_load(sB + s * TC_KB_BYTES, tsrc + (size_t)it * TC_KB_BYTES, TC_KB_BYTES, bar_full + 8 * s);
+#ifdef CLB_LAB
+                if (LAB && dbg == 7 && qblock == 0 && tile0 == 0 && (it & 1) && (it >> 1) < 256) g_tc_trace[0][it >> 1] = clock64();
+#endif
             }
             __syncwarp();
         }
@@ -979,6 +991,9 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                     tc_commit(bar_tfull + 16 * m);
                     tc_commit(bar_empty + 8 * s0);
                     tc_commit(bar_empty + 8 * s1);
+#ifdef CLB_LAB
+                    if (LAB && dbg == 7 && qblock == 0 && tile0 == 0 && m == 0 && j < 256) g_tc_trace[1][j] = clock64();
+#endif
                 }
                 __syncwarp();
             } else {
@@ -1074,10 +1089,20 @@ tc4_cta(const uint32_t* __restrict__ Q, int nQ, const uint8_t* __restrict__ Tx, 
                 continue;
             }
             if (prof && j < 2) pc[2 + j] = clock64();
+#ifdef CLB_LAB
+            if (prof && j < 256) g_tc_trace[2][j] = clock64();
+#endif
             const int valid = chunk_rows - j * TC_TILE - half * 64;       // rows of this half that exist
             const uint32_t row0 = (uint32_t)(j * TC_TILE + half * 64);
+#ifdef CLB_LAB
+            long long* tr = (prof && j < 256) ? &g_tc_trace[4][j] : nullptr;
+            if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + hb, lane, st, tr);
+            else             tc_epilogue_half_tile<true>(tbase, row0, valid, bar_tempty + hb, lane, st, tr);
+            if (prof && j < 256) g_tc_trace[3][j] = clock64();
+#else
             if (valid >= 64) tc_epilogue_half_tile<false>(tbase, row0, 64, bar_tempty + hb, lane, st);
             else             tc_epilogue_half_tile<true>(tbase, row0, valid, bar_tempty + hb, lane, st);
+#endif
         }
         // merge the two column halves of each query by packed key.  The staging array aliases ring stage 0, which the
         // last tile's MMAs of the OTHER query tile may still be reading: wait until every epilogue warp has seen its last tile.
@@ -1260,6 +1285,14 @@ int microbench_mma(double* out6) {
     out6[3] = 2.0 * mac * mmas * sms / (ms * 1e-3) / 1e12; out6[4] = sms; out6[5] = mmas;
     return CLB_OK;
 }
+
+#ifdef CLB_LAB
+int tc_lab_tile_clocks(long long* out1024) {
+    CLB_CUDA(cudaDeviceSynchronize());
+    CLB_CUDA(cudaMemcpyFromSymbol(out1024, g_tc_trace, sizeof(long long) * 6 * 256));
+    return CLB_OK;
+}
+#endif
 
 // ---- host side --------------------------------------------------------------------------------
 bool tc_wanted(int nQ, int nT) {
