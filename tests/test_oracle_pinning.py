@@ -109,6 +109,36 @@ def test_fast_shift_ub_edge(ref_cpu, w):
     assert ((s1 == s0) | (s1 == 0)).all() and (s0[:, : w - 35] == s1[:, : w - 35]).all()
 
 
+def _fast_cases(n, seed):
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        w = int(38 + 16 * rng.integers(0, 40)) if i % 2 == 0 else int(rng.integers(7, 700))     # every other width sits on the `1 << 32` edge
+        out.append((w, int(rng.integers(7, 260)), int(rng.integers(1, 90)), int(rng.integers(0, 3)), 100 + i))
+    return out
+
+
+@pytest.mark.parametrize("w,h,thr,kind,seed", _fast_cases(48, 11))
+def test_fast_random_sizes_match_reference(ref_cpu, w, h, thr, kind, seed):
+    """seeded random widths / heights / thresholds, half of them on widths with (w - 38) % 16 == 0: the restatement with the
+    reference's column walk (quirk = 1) equals the compiled KFAST.h, keypoint for keypoint, on textured, noisy and nearly flat images"""
+    O = ref_cpu
+    if kind == 0:
+        img = synth.textured_frame(w, h, seed)
+    elif kind == 1:
+        img = np.random.default_rng(seed).integers(0, 256, (h, w), dtype=np.uint8)
+    else:                                                   # flat with a few bright blobs: most rows have no pre-test pass at all
+        img = np.full((h, w), 100, np.uint8)
+        rng = np.random.default_rng(seed)
+        for _ in range(6):
+            y, x = int(rng.integers(0, h)), int(rng.integers(0, w))
+            img[max(0, y - 2):y + 3, max(0, x - 2):x + 3] = 250
+    ref = O.ref_kfast(img, thr, multithread=False)
+    assert np.array_equal(ref, O.fast_nms(img, thr, quirk=1)), (w, h, thr, kind)
+    if w >= 38 and (w - 38) % 16 != 0:
+        assert np.array_equal(ref, O.fast_nms(img, thr, quirk=0))
+
+
 def test_noise_image(ref_cpu):
     O = ref_cpu
     img = np.random.default_rng(0).integers(0, 256, (480, 640), dtype=np.uint8)
