@@ -254,8 +254,9 @@ def _gold(name):
     return np.load(p)
 
 
-def test_golden_detect_describe(oracle):
-    g = _gold("frame168.npz")
+@pytest.mark.parametrize("name", ["frame168.npz", "frame214.npz"])      # frame214: levels 214 and 86 wide sit on the KFAST.h:243 edge
+def test_golden_detect_describe(oracle, name):
+    g = _gold(name)
     kps, desc, pyr = oracle.detect_describe(g["img"], thresh=int(g["thresh"]), want_pyramid=True)
     assert np.array_equal(kps.view(np.uint8), g["kps"].view(np.uint8))
     assert np.array_equal(desc, g["desc"])

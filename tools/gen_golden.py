@@ -15,6 +15,32 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 os.makedirs(GOLD, exist_ok=True)
 assert O.ref_cpu() is not None, "build oracle/_ref first (make -C oracle ref_cpu)"
 
+
+
+def gen_frame(name, w, h, seed, thresh, need_quirk):
+    """one small frame through the whole detect + describe restatement, every level's keypoints + angles cross-checked against the
+    reference's compiled CPU code before anything is written"""
+    img = synth.textured_frame(w, h, seed)
+    kps, desc, pyr = O.detect_describe(img, thresh=thresh, want_pyramid=True)
+    bites = False
+    for L, lv in enumerate(pyr):
+        ref = O.ref_kfast(lv, thresh)
+        mine = kps[kps["scale"] == L]
+        assert len(ref) == len(mine) and np.array_equal(ref["x"], mine["x"]) and np.array_equal(ref["y"], mine["y"]) \
+            and np.array_equal(ref["score"], mine["score"]), L
+        for k in mine:
+            assert np.float32(O.ref_feature_angle(lv, k["x"], k["y"])).view(np.uint32) == k["angle"].view(np.uint32)
+        bites = bites or not np.array_equal(O.fast_nms(lv, thresh, quirk=0), O.fast_nms(lv, thresh, quirk=1))
+    assert bites == need_quirk, "the frame must (not) have a level on which KFAST.h:243 drops columns"
+    np.savez_compressed(os.path.join(GOLD, name), img=img, thresh=thresh, kps=kps, desc=desc,
+                        pyr_sha256=hashlib.sha256(b"".join(p.tobytes() for p in pyr)).hexdigest())
+    print(name, len(kps), "keypoints; levels", [lv.shape[1] for lv in pyr])
+
+
+if "frame214" in sys.argv[1:]:          # only the fixture added in round 2: level 0 is 214 px wide, (214 - 38) % 16 == 0
+    gen_frame("frame214.npz", 214, 161, 78, 20, True)
+    sys.exit(0)
+
 img = synth.textured_frame(168, 126, 77)
 thresh = 20
 kps, desc, pyr = O.detect_describe(img, thresh=thresh, want_pyramid=True)
